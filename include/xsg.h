@@ -1,0 +1,149 @@
+/*
+ * xsg.h -- C ABI of the B200 scan-and-match library (libxsg.so).
+ *
+ * This is the drop-in boundary: plain C types, opaque handles, 0 / negative status codes.
+ * Everything below replaces, for the literal (non-regex, case-sensitive) path, what the
+ * reference does on CPU threads:
+ *
+ *   xsg_scan / xsg_search_host
+ *        <- the per-chunk matchers   src/string_search/simd_search.cpp:116-204,289-336
+ *        <- the chunk wrappers       include/xsearch/string_search/search_wrappers.h:29-52,111-207
+ *        <- the searcher functors    include/xsearch/tasks/searchers.h:38-92
+ *        <- the worker loop          include/xsearch/Searcher.h:100-120  (chunk -> search -> result)
+ *   xsg_result_*
+ *        <- the result collector     include/xsearch/ResultTypes.h:31-130
+ *   xsg_corpus_chunk / xsg_chunk_bounds_host
+ *        <- the v1 chunker (>= 16 MiB, extended through the next '\n'); evidence
+ *           test/files/sample.meta + metafile_cat.cpp:39-49
+ *   xsg_search_host
+ *        <- the reader stage         include/xsearch/tasks/readers.h:39-48 (pinned, double-buffered H2D)
+ *
+ * The C++ surface users see (xs::extern_search<Tag>, Searcher::join(), getResult()) lives in
+ * include/xsearch_b200/xsearch.hpp and only calls the functions declared here.
+ *
+ * Semantics are bit-exact with the reference, including the scalar-tail quirk of
+ * simd::strstr in the last 31+m bytes of every reference chunk (simd_search.cpp:58-78,169-171,203).
+ * Requirements: 1 <= m <= XSG_MAX_PATTERN, the pattern holds no '\n', and every reference-chunk
+ * boundary except the last lies directly behind a '\n' (the v1 chunker guarantees it).
+ *
+ * Threading: a context may be driven by one host thread at a time.
+ */
+#ifndef XSG_H
+#define XSG_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XSG_MAX_PATTERN 64u
+#define XSG_DEFAULT_MIN_CHUNK 16777216ull /* v1 chunk size, SURVEY.md 3.5 */
+
+/* result kinds == the reference's tag types (README.md:72-81) */
+enum {
+  XSG_COUNT = 1u << 0,              /* xs::count            : greedy non-overlapping matches       */
+  XSG_COUNT_LINES = 1u << 1,        /* xs::count_lines      : lines holding >= 1 match             */
+  XSG_MATCH_BYTE_OFFSETS = 1u << 2, /* xs::match_byte_offsets : global offset of every match       */
+  XSG_LINE_BYTE_OFFSETS = 1u << 3,  /* xs::line_byte_offsets  : global offset of matching lines    */
+  XSG_LINE_INDICES = 1u << 4,       /* xs::line_indices       : 0-based index of matching lines    */
+  XSG_LINES = 1u << 5               /* xs::lines : (start, length) of matching lines, '\n' excluded */
+};
+
+/* status codes */
+enum {
+  XSG_OK = 0,
+  XSG_ERR_CUDA = -1,     /* CUDA runtime failure, see xsg_last_error() */
+  XSG_ERR_ARG = -2,      /* bad argument (m == 0, m > 64, '\n' in pattern, unknown kind ...) */
+  XSG_ERR_BOUNDS = -3,   /* chunk bounds not increasing / not newline-aligned / not ending at n */
+  XSG_ERR_NOMEM = -4,    /* device or host allocation failed */
+  XSG_ERR_STATE = -5     /* call order (e.g. scan before bounds were set) */
+};
+
+typedef struct xsg_ctx xsg_ctx;       /* one device + stream + scratch */
+typedef struct xsg_corpus xsg_corpus; /* device-resident bytes + reference-chunk bounds */
+typedef struct xsg_result xsg_result; /* device-resident result vectors of one scan */
+
+typedef struct xsg_scan_opts {
+  uint64_t global_offset_base; /* added to every byte offset (shard / segment base)           */
+  uint64_t line_index_base;    /* added to every line index ('\n' count before this corpus)   */
+  uint64_t occ_capacity;       /* 0 = automatic; max raw occurrences buffered on the device   */
+} xsg_scan_opts;
+
+typedef struct xsg_timings {
+  float scan_ms;        /* all device work of the scan (CUDA events on the library's stream) */
+  float main_kernel_ms; /* the byte-scanning kernel alone                                     */
+  float post_ms;        /* list-domain kernels (tail emulation, line selection, compaction)   */
+  float h2d_ms;         /* xsg_search_host only: wall time of the streamed pipeline           */
+  uint32_t kernel_launches; /* kernels launched by the library for this scan                  */
+  uint32_t reserved;
+} xsg_timings;
+
+/* parameters of the deterministic synthetic corpus (block-wise pure function of seed, block) */
+typedef struct xsg_synth_params {
+  uint64_t seed;
+  uint32_t needle_len;           /* 0 = no needle */
+  uint8_t needle[XSG_MAX_PATTERN];
+  uint32_t needle_rate_u32;      /* per line: inject when rand32 < rate (0 = never) */
+} xsg_synth_params;
+#define XSG_SYNTH_BLOCK 4096u /* every synthetic block is this long and ends with '\n' */
+
+const char* xsg_last_error(void);
+int xsg_version(void);
+
+/* ---- context -------------------------------------------------------------------------- */
+int xsg_init(int device, xsg_ctx** out);
+void xsg_destroy(xsg_ctx* ctx);
+int xsg_device_info(xsg_ctx* ctx, int* sm_count, uint64_t* total_mem, char* name, size_t name_cap);
+
+/* pinned host memory for xsg_search_host / xsg_corpus_upload sources (cudaHostAlloc) */
+int xsg_host_alloc(uint64_t n, void** out);
+void xsg_host_free(void* p);
+
+/* ---- corpus (device-resident) ----------------------------------------------------------- */
+int xsg_corpus_alloc(xsg_ctx* ctx, uint64_t n, xsg_corpus** out);
+/* borrow caller-owned device memory (16-byte aligned, readable up to the next 16-byte boundary) */
+int xsg_corpus_wrap(xsg_ctx* ctx, const void* dev_ptr, uint64_t n, xsg_corpus** out);
+void xsg_corpus_free(xsg_corpus* c);
+uint64_t xsg_corpus_size(const xsg_corpus* c);
+const void* xsg_corpus_device_ptr(const xsg_corpus* c);
+int xsg_corpus_upload(xsg_corpus* c, const void* host, uint64_t offset, uint64_t n);
+int xsg_corpus_download(const xsg_corpus* c, void* host, uint64_t offset, uint64_t n);
+/* fill [0, size) with synthetic blocks first_block, first_block+1, ... (size % XSG_SYNTH_BLOCK == 0) */
+int xsg_corpus_fill_synth(xsg_corpus* c, uint64_t first_block, const xsg_synth_params* p);
+/* reference chunks: either computed on the device with the v1 rule, or supplied */
+int xsg_corpus_chunk(xsg_corpus* c, uint64_t min_chunk);
+int xsg_corpus_set_bounds(xsg_corpus* c, const uint64_t* bounds, uint64_t nb);
+uint64_t xsg_corpus_num_chunks(const xsg_corpus* c);
+int xsg_corpus_get_bounds(const xsg_corpus* c, uint64_t* bounds, uint64_t cap);
+
+/* ---- host-side helpers (same arithmetic as the device paths; no GPU needed) --------------- */
+void xsg_synth_host(void* dst, uint64_t first_block, uint64_t n_blocks, const xsg_synth_params* p);
+uint64_t xsg_chunk_bounds_host(const void* buf, uint64_t n, uint64_t min_chunk, uint64_t* bounds, uint64_t cap);
+
+/* ---- scan ------------------------------------------------------------------------------- */
+/* device-resident corpus; kinds = OR of XSG_* result kinds; opts may be NULL */
+int xsg_scan(xsg_ctx* ctx, const xsg_corpus* c, const uint8_t* pattern, uint32_t m, uint32_t kinds,
+             const xsg_scan_opts* opts, xsg_result** out);
+/* host buffer (pinned or pageable), streamed through double-buffered device segments of whole
+ * reference chunks; bounds may be NULL (v1 rule with min_chunk, 0 = default) */
+int xsg_search_host(xsg_ctx* ctx, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb,
+                    uint64_t min_chunk, const uint8_t* pattern, uint32_t m, uint32_t kinds,
+                    const xsg_scan_opts* opts, xsg_result** out);
+
+/* ---- results ---------------------------------------------------------------------------- */
+uint64_t xsg_result_count(const xsg_result* r, uint32_t kind);
+/* copy up to cap values of one vector kind to host memory (XSG_LINES: line starts) */
+int xsg_result_copy(const xsg_result* r, uint32_t kind, uint64_t* dst, uint64_t cap);
+int xsg_result_copy_line_lengths(const xsg_result* r, uint64_t* dst, uint64_t cap);
+/* device pointer of a result vector (stays valid until xsg_result_free) */
+const uint64_t* xsg_result_device_ptr(const xsg_result* r, uint32_t kind);
+uint64_t xsg_result_newlines(const xsg_result* r);        /* '\n' in the scanned bytes (line kinds) */
+uint64_t xsg_result_raw_occurrences(const xsg_result* r); /* all true occurrences seen            */
+int xsg_result_timings(const xsg_result* r, xsg_timings* t);
+void xsg_result_free(xsg_result* r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,262 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same inputs, bit-exact."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import gen_cases
+import oracle_lib
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+ALL = None
+
+
+@pytest.fixture(scope="module")
+def xs():
+    import xsearch_b200
+    return xsearch_b200
+
+
+@pytest.fixture(scope="module")
+def ctx(xs):
+    c = xs.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    o, _ = oracle_lib.load(build=False)
+    return o
+
+
+def all_kinds(xs):
+    return xs.COUNT | xs.COUNT_LINES | xs.MATCH_BYTE_OFFSETS | xs.LINE_BYTE_OFFSETS | xs.LINE_INDICES | xs.LINES
+
+
+def expected(oracle, buf, pat, bounds):
+    st, ln = oracle.lines(buf, pat, bounds)
+    return {
+        "count": oracle.count(buf, pat, bounds, False),
+        "count_lines": oracle.count(buf, pat, bounds, True),
+        "match": oracle.match_byte_offsets(buf, pat, bounds),
+        "line_off": oracle.line_byte_offsets(buf, pat, bounds),
+        "line_idx": oracle.line_indices(buf, pat, bounds),
+        "lines": (st, ln),
+    }
+
+
+def check_result(xs, res, exp, tag):
+    assert res.count(xs.COUNT) == exp["count"], tag
+    assert res.count(xs.COUNT_LINES) == exp["count_lines"], tag
+    assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp["match"]), tag
+    assert np.array_equal(res.vector(xs.LINE_BYTE_OFFSETS), exp["line_off"]), tag
+    assert np.array_equal(res.vector(xs.LINE_INDICES), exp["line_idx"]), tag
+    st, ln = res.line_spans()
+    assert np.array_equal(st, exp["lines"][0]) and np.array_equal(ln, exp["lines"][1]), tag
+
+
+def run_case(xs, ctx, oracle, buf, pat, bounds, tag, exp=None):
+    exp = exp or expected(oracle, buf, pat, bounds)
+    corpus = ctx.corpus_from_host(buf, bounds=bounds)
+    try:
+        res = ctx.scan(corpus, pat, all_kinds(xs))
+        check_result(xs, res, exp, tag)
+        res.free()
+        # the count-only fast path (no occurrence list) must agree as well
+        res = ctx.scan(corpus, pat, xs.COUNT)
+        assert res.count(xs.COUNT) == exp["count"], ("count-only", tag)
+        res.free()
+        res = ctx.scan(corpus, pat, xs.COUNT_LINES | xs.LINE_INDICES)
+        assert res.count(xs.COUNT_LINES) == exp["count_lines"], tag
+        assert np.array_equal(res.vector(xs.LINE_INDICES), exp["line_idx"]), tag
+        res.free()
+    finally:
+        corpus.free()
+
+
+def test_reference_kats(xs, ctx, oracle):
+    kat = json.load(open(os.path.join(GOLD, "kat.json")))
+    text = np.frombuffer(open(os.path.join(GOLD, "wrappers_dummy_text.bin"), "rb").read(), dtype=np.uint8)
+    w = kat["wrappers"]
+    corpus = ctx.corpus_from_host(text, bounds=np.array([text.size], dtype=np.uint64))
+    res = ctx.scan(corpus, w["pattern"].encode(), all_kinds(xs))
+    assert list(res.vector(xs.MATCH_BYTE_OFFSETS)) == w["byte_offsets_match"]   # search_wrappersTest.cpp:26
+    assert list(res.vector(xs.LINE_BYTE_OFFSETS)) == w["byte_offsets_line"]     # :39
+    assert res.count(xs.COUNT_LINES) == w["count"]                              # :52
+    st, ln = res.line_spans()
+    assert [text[int(s):int(s) + int(l)].tobytes().decode() for s, l in zip(st, ln)] == w["lines"]
+    res.free()
+    corpus.free()
+    text = np.frombuffer(open(os.path.join(GOLD, "simd_dummy_text.bin"), "rb").read(), dtype=np.uint8)
+    corpus = ctx.corpus_from_host(text, bounds=np.array([text.size], dtype=np.uint64))
+    for pat, want in kat["findAll"]:                                            # simd_searchTest.cpp:93-98
+        r = ctx.scan(corpus, pat.encode("latin-1"), xs.COUNT)
+        assert r.count(xs.COUNT) == want, pat
+        r.free()
+    for pat, want in kat["findAllPerLine"]:                                     # simd_searchTest.cpp:84-89
+        r = ctx.scan(corpus, pat.encode("latin-1"), xs.COUNT_LINES)
+        assert r.count(xs.COUNT_LINES) == want, pat
+        r.free()
+    corpus.free()
+
+
+def test_golden_reference_vectors(xs, ctx, oracle):
+    data = json.load(open(os.path.join(GOLD, "ref_vectors.json")))
+    for v in data["vectors"]:
+        buf, pat, bounds = gen_cases.materialize(v["case"])
+        if buf.size == 0:
+            continue
+        exp = {
+            "count": v["count"], "count_lines": v["count_lines"],
+            "match": np.array(v["match_byte_offsets"], dtype=np.uint64),
+            "line_off": np.array(v["line_byte_offsets"], dtype=np.uint64),
+            "line_idx": np.array(v["line_indices"], dtype=np.uint64),
+            "lines": (np.array([a for a, _ in v["lines"]], dtype=np.uint64),
+                      np.array([b for _, b in v["lines"]], dtype=np.uint64)),
+        }
+        run_case(xs, ctx, oracle, buf, pat, bounds, v["case"], exp)
+
+
+def test_random_differential(xs, ctx, oracle):
+    for case in gen_cases.random_cases(400, seed0=21, max_n=6000):
+        buf, pat, bounds = gen_cases.materialize(case)
+        if buf.size == 0:
+            continue
+        run_case(xs, ctx, oracle, buf, pat, bounds, case)
+
+
+@pytest.mark.parametrize("m", [1, 2, 3, 4, 5, 7, 8, 9, 16, 31, 32, 33, 63, 64])
+def test_pattern_lengths_and_tile_edges(xs, ctx, oracle, m):
+    rng = np.random.default_rng(m)
+    base = "Sherlock Holmes and the hound of the Baskervilles went home!!!xyz"
+    pat = base[:m].encode()
+    # sizes around the 32 KiB tile and 4 KiB granule edges, hits straddling every boundary
+    for n in (m, m + 1, 4095, 4096, 4097, 32767, 32768, 32769, 32768 + 15, 32768 + 17, 3 * 32768 + 5, 200000):
+        if n < m:
+            continue
+        buf = gen_cases._random_text(rng, n, b"abcdefgh tS\n", 0.03)
+        p = np.frombuffer(pat, dtype=np.uint8)
+        for edge in (4096, 32768, 65536, 98304, n):
+            for d in (-m - 1, -m, -m + 1, -1, 0, 1):
+                pos = edge + d
+                if 0 <= pos and pos + m <= n:
+                    buf[pos:pos + m] = p
+        for _ in range(20):
+            pos = int(rng.integers(0, n - m + 1))
+            buf[pos:pos + m] = p
+        bounds = gen_cases._chunk_bounds(buf, 20000)
+        run_case(xs, ctx, oracle, buf, pat, bounds, ("edges", m, n))
+
+
+def test_special_bytes_and_lines(xs, ctx, oracle):
+    rng = np.random.default_rng(5)
+    # CRLF, empty lines, bytes >= 0x80, a NUL in the pattern, no trailing newline, one very long line
+    texts = [
+        (b"line one\r\n\r\n\r\nneedle here\r\nneedle again needle\r\n\r\nlast needle", b"needle"),
+        (b"\n\n\n\n", b"x"),
+        (b"\xe9\xfc\xe9\xfc\n\xe9\xfc\xff\x80\n", b"\xe9\xfc"),
+        (b"ab\x00cd\nab\x00cd ab\x00cd\n\x00\x00\x00", b"b\x00c"),
+        (b"\x00" * 100 + b"\n", b"\x00\x00"),
+        (b"x" * 70000 + b"needle" + b"y" * 70000 + b"needle\nneedle", b"needle"),
+    ]
+    for text, pat in texts:
+        buf = np.frombuffer(text, dtype=np.uint8).copy()
+        for min_chunk in (16, 1 << 20):
+            bounds = gen_cases._chunk_bounds(buf, min_chunk)
+            run_case(xs, ctx, oracle, buf, pat, bounds, (text[:20], pat, min_chunk))
+    # pattern longer than the corpus
+    buf = np.frombuffer(b"short\n", dtype=np.uint8).copy()
+    run_case(xs, ctx, oracle, buf, b"much longer than the text", np.array([6], dtype=np.uint64), "longpat")
+    del rng
+
+
+def test_synthetic_corpus_device_equals_host(xs, ctx, oracle):
+    p = xs.SynthParams.make(42, b"Sherlock", 30.0 / 8192)
+    n = 4096 * 3000
+    corpus = ctx.corpus(n)
+    corpus.fill_synth(p)
+    host = xs.synth_host(n, p)
+    assert np.array_equal(corpus.download(), host)
+    # device chunker == host chunker == oracle chunker
+    corpus.chunk(1 << 20)
+    assert np.array_equal(corpus.bounds(), oracle.chunk_bounds(host, 1 << 20))
+    assert np.array_equal(corpus.bounds(), xs.chunk_bounds_host(host, 1 << 20))
+    for pat in (b"Sherlock", b"the", b"e", b"th", b"that", b" and the "):
+        exp = expected(oracle, host, pat, corpus.bounds())
+        res = ctx.scan(corpus, pat, all_kinds(xs))
+        check_result(xs, res, exp, pat)
+        res.free()
+    corpus.free()
+
+
+def test_bad_arguments(xs, ctx):
+    buf = np.frombuffer(b"hello\nworld\n", dtype=np.uint8).copy()
+    corpus = ctx.corpus(buf.size)
+    corpus.upload(buf)
+    with pytest.raises(xs.XsgError):
+        ctx.scan(corpus, b"x", xs.COUNT)                       # bounds not set
+    with pytest.raises(xs.XsgError):
+        corpus.set_bounds(np.array([3, 12], dtype=np.uint64))   # not newline-aligned
+    with pytest.raises(xs.XsgError):
+        corpus.set_bounds(np.array([6, 11], dtype=np.uint64))   # does not end at n
+    corpus.set_bounds(np.array([6, 12], dtype=np.uint64))
+    with pytest.raises(xs.XsgError):
+        ctx.scan(corpus, b"", xs.COUNT)
+    with pytest.raises(xs.XsgError):
+        ctx.scan(corpus, b"a\nb", xs.COUNT)
+    with pytest.raises(xs.XsgError):
+        ctx.scan(corpus, b"x" * 65, xs.COUNT)
+    with pytest.raises(xs.XsgError):
+        ctx.scan(corpus, b"x", 0)
+    r = ctx.scan(corpus, b"o", xs.COUNT)
+    assert r.count(xs.COUNT) == 2
+    r.free()
+    corpus.free()
+
+
+def test_streamed_host_search(xs, ctx, oracle, monkeypatch):
+    monkeypatch.setenv("XSG_SEGMENT_MB", "1")
+    p = xs.SynthParams.make(7, b"needle-needle-needle-needle-0032", 30.0 / 16384)
+    host = xs.synth_host(4096 * 2500, p)  # ~10 MB -> ~10 segments of ~1 MiB
+    for pat, min_chunk in ((b"needle-needle-needle-needle-0032", 300000), (b"the", 1 << 20), (b"Sherlock", 70000)):
+        bounds = oracle.chunk_bounds(host, min_chunk)
+        exp = expected(oracle, host, pat, bounds)
+        res = ctx.search_host(host, None, pat, all_kinds(xs), min_chunk=min_chunk)
+        check_result(xs, res, exp, ("stream", pat))
+        assert res.newlines == int((host == 10).sum())
+        res.free()
+        res = ctx.search_host(host, None, pat, all_kinds(xs), bounds=bounds, offset_base=1000, line_index_base=77)
+        assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp["match"] + np.uint64(1000))
+        assert np.array_equal(res.vector(xs.LINE_INDICES), exp["line_idx"] + np.uint64(77))
+        res.free()
+
+
+def test_large_properties(xs, ctx):
+    """Size-independent properties at a size the oracle would need minutes for."""
+    n = 4096 * 262144  # 1 GiB
+    rate = 30.0 / 65536
+    p = xs.SynthParams.make(2, b"Sherlock", rate)
+    corpus = ctx.corpus(n)
+    corpus.fill_synth(p)
+    corpus.chunk()
+    res = ctx.scan(corpus, b"Sherlock", all_kinds(xs))
+    cnt, cl = res.count(xs.COUNT), res.count(xs.COUNT_LINES)
+    m = res.vector(xs.MATCH_BYTE_OFFSETS)
+    lo, li = res.vector(xs.LINE_BYTE_OFFSETS), res.vector(xs.LINE_INDICES)
+    st, ln = res.line_spans()
+    assert cnt == m.size and cl == lo.size == li.size == st.size
+    assert cnt >= cl > 0.5 * n / 65536
+    assert (np.diff(m.astype(np.int64)) >= 8).all()          # sorted, non-overlapping
+    assert (np.diff(lo.astype(np.int64)) > 0).all() and (np.diff(li.astype(np.int64)) > 0).all()
+    assert np.array_equal(st, lo)
+    # every reported line really contains the needle and is newline-delimited
+    for s, l in list(zip(st, ln))[:200]:
+        line = corpus.download(int(s), int(l) + 1).tobytes()
+        assert b"Sherlock" in line and line.endswith(b"\n") and b"\n" not in line[:-1]
+    # shards: the same corpus scanned as two halves with bases equals the whole
+    res.free()
+    corpus.free()

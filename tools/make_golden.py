@@ -1,0 +1,102 @@
+#!/usr/bin/env python3
+"""Builds tests/golden/ from the reference tree (run in the container that has /root/reference).
+
+  * simd_dummy_text.bin / wrappers_dummy_text.bin : the two fixture texts of the reference's unit tests,
+    extracted from the C string literals at test/src/string_search/simd_searchTest.cpp:12-34 and
+    test/src/string_search/search_wrappersTest.cpp:12-21
+  * kat.json      : the expected values those tests assert (file:line noted per entry)
+  * ref_vectors.json : outputs of the reference's own code (oracle/_ref/libxsref.so) on small seeded
+    adversarial inputs -- inputs are regenerated from the seed by tests/gen_cases.py
+"""
+import json
+import os
+import re
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+REF = "/root/reference"
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def c_literal(path, start_marker):
+    src = open(path, encoding="utf-8").read()
+    i = src.index(start_marker)
+    j = src.index(";", i)
+    body = src[i:j]
+    out = bytearray()
+    for lit in re.findall(r'"((?:[^"\\]|\\.)*)"', body):
+        k = 0
+        while k < len(lit):
+            ch = lit[k]
+            if ch == "\\":
+                nxt = lit[k + 1]
+                if nxt == "n":
+                    out.append(10)
+                    k += 2
+                elif nxt in "01234567":
+                    m = re.match(r"[0-7]{1,3}", lit[k + 1:])
+                    out.append(int(m.group(0), 8))
+                    k += 1 + len(m.group(0))
+                else:
+                    out.append(ord(nxt))
+                    k += 2
+            else:
+                out += ch.encode()
+                k += 1
+    return bytes(out)
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    simd = c_literal(os.path.join(REF, "test/src/string_search/simd_searchTest.cpp"), "static char dummy_text[1241]")
+    assert len(simd) == 1240, len(simd)
+    wrap = c_literal(os.path.join(REF, "test/src/string_search/search_wrappersTest.cpp"), "static char dummy_text[]")
+    open(os.path.join(GOLD, "simd_dummy_text.bin"), "wb").write(simd)
+    open(os.path.join(GOLD, "wrappers_dummy_text.bin"), "wb").write(wrap)
+    long_pat = ("smooth-bellied chirognostic inkos BVM antigraphy pagne "
+                "bicorne complementizer commorant ever-endingly sheikhly")
+    soh = "\\u0001"  # the tests use the byte \1 as an end marker; kept escaped in JSON
+    kat = {
+        "source": "lfreist/x-search test/src/string_search/{simd_searchTest,search_wrappersTest}.cpp",
+        "findNext": [  # simd_searchTest.cpp:63-73
+            ["Liane", 0, 0], [long_pat, 0, 113], ["Helladic", 0, 346], ["ly\x01", 0, 1237],
+            ["jkahgsf", 0, -1], ["ia", 0, 1], ["ia", 3, 455]],
+        "findNextNewLine": [[0, 223], [224, 282], [283, 728], [729, -1]],  # :77-80
+        "findAllPerLine": [["is", 2], ["th", 3], ["Van", 1], ["y\x01", 1], ["Liane", 1], ["Vansdf", 0]],  # :84-89
+        "findAll": [["is", 8], ["th", 5], ["Van", 1], ["y\x01", 1], ["Liane", 1], ["Vansdf", 0]],  # :93-98
+        "wrappers": {  # search_wrappersTest.cpp:26,39,52 and the line contents of :64-69 without '\n'
+            "pattern": "ant", "byte_offsets_match": [2, 151, 197, 507], "byte_offsets_line": [0, 113, 176, 460],
+            "count": 4,
+            "lines": ["Liant reindorsing two-time zippering chromolithography rainbowweed",
+                      "smooth-bellied chirognostic inkos BVM antigraphy pagne bicorne",
+                      "complementizer commorant ever-endingly sheikhly",
+                      "refrangible terebras autobiographal mid-breast ant"]},
+    }
+    del soh
+    json.dump(kat, open(os.path.join(GOLD, "kat.json"), "w"), indent=1)
+
+    import gen_cases
+    import oracle_lib
+    _, ref = oracle_lib.load()
+    assert ref is not None, "build oracle/_ref first (make -C oracle)"
+    vecs = []
+    for case in gen_cases.golden_cases():
+        buf, pat, bounds = gen_cases.materialize(case)
+        st, ln = ref.lines(buf, pat, bounds)
+        vecs.append({
+            "case": case,
+            "count": int(ref.count(buf, pat, bounds, False)),
+            "count_lines": int(ref.count(buf, pat, bounds, True)),
+            "match_byte_offsets": [int(x) for x in ref.match_byte_offsets(buf, pat, bounds)],
+            "line_byte_offsets": [int(x) for x in ref.line_byte_offsets(buf, pat, bounds)],
+            "line_indices": [int(x) for x in ref.line_indices(buf, pat, bounds)],
+            "lines": [[int(a), int(b)] for a, b in zip(st, ln)],
+        })
+    json.dump({"generator": "tools/make_golden.py via oracle/_ref/libxsref.so (reference @ 86641bb)", "vectors": vecs},
+              open(os.path.join(GOLD, "ref_vectors.json"), "w"))
+    print("golden: %d KAT groups, %d reference vectors" % (len(kat) - 1, len(vecs)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,319 @@
+"""Host-side mirror of the reference interface for the scan-and-match path, on top of the C ABI.
+
+Reference shapes kept (file:line in /root/reference):
+  * ``extern_search<Tag>(pattern, file, meta_file, num_threads, max_num_readers)`` -> Searcher whose
+    work has already started (README.md:72-83, checkit.cpp:4)
+  * ``Searcher::join()`` idempotent, destructor joins (include/xsearch/Searcher.h:41,52-59)
+  * ``getResult()``: ``size()``, ``copyResultSafe()``, blocking iteration; count tags iterate running
+    totals whose last value is the total (include/xsearch/ResultTypes.h:48-60,
+    test/src/xsearchTest.cpp:346,450,735-739)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Iterator, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import (COUNT, COUNT_LINES, DEFAULT_MIN_CHUNK, LINE_BYTE_OFFSETS, LINE_INDICES, LINES,
+               MATCH_BYTE_OFFSETS, SYNTH_BLOCK, TAGS, ScanOpts, SynthParams, Timings, XsgError, _check, lib)
+
+_PU64 = C.POINTER(C.c_uint64)
+_VECTOR_KINDS = (MATCH_BYTE_OFFSETS, LINE_BYTE_OFFSETS, LINE_INDICES, LINES)
+
+
+def _u64ptr(a: np.ndarray):
+    assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_PU64)
+
+
+def synth_host(n_bytes: int, params: SynthParams, first_block: int = 0) -> np.ndarray:
+    """Synthetic corpus on the host (same bytes as Corpus.fill_synth on the device)."""
+    assert n_bytes % SYNTH_BLOCK == 0
+    out = np.empty(n_bytes, dtype=np.uint8)
+    lib.xsg_synth_host(out.ctypes.data, first_block, n_bytes // SYNTH_BLOCK, C.byref(params))
+    return out
+
+
+def chunk_bounds_host(buf: np.ndarray, min_chunk: int = DEFAULT_MIN_CHUNK) -> np.ndarray:
+    """v1 chunking rule (>= min_chunk bytes, extended through the next newline) on a host buffer."""
+    n = int(buf.size)
+    nb = lib.xsg_chunk_bounds_host(buf.ctypes.data, n, min_chunk, None, 0)
+    out = np.empty(nb, dtype=np.uint64)
+    if nb:
+        lib.xsg_chunk_bounds_host(buf.ctypes.data, n, min_chunk, _u64ptr(out), nb)
+    return out
+
+
+class Context:
+    """One device + the library's streams and scratch (xsg_ctx)."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        _check(lib.xsg_init(device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def close(self) -> None:
+        if self._h:
+            lib.xsg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def device_info(self) -> dict:
+        sm, mem, name = C.c_int(), C.c_uint64(), C.create_string_buffer(128)
+        _check(lib.xsg_device_info(self._h, C.byref(sm), C.byref(mem), name, 128))
+        return {"sm_count": sm.value, "total_mem": mem.value, "name": name.value.decode()}
+
+    # -- corpora ----------------------------------------------------------------------------
+    def corpus(self, n_bytes: int) -> "Corpus":
+        h = C.c_void_p()
+        _check(lib.xsg_corpus_alloc(self._h, n_bytes, C.byref(h)))
+        return Corpus(self, h, n_bytes)
+
+    def corpus_from_host(self, buf: np.ndarray, bounds: Optional[np.ndarray] = None,
+                         min_chunk: int = DEFAULT_MIN_CHUNK) -> "Corpus":
+        c = self.corpus(int(buf.size))
+        c.upload(buf)
+        if bounds is None:
+            c.chunk(min_chunk)
+        else:
+            c.set_bounds(bounds)
+        return c
+
+    def wrap(self, dev_ptr: int, n_bytes: int) -> "Corpus":
+        h = C.c_void_p()
+        _check(lib.xsg_corpus_wrap(self._h, C.c_void_p(dev_ptr), n_bytes, C.byref(h)))
+        return Corpus(self, h, n_bytes)
+
+    # -- searches ---------------------------------------------------------------------------
+    def scan(self, corpus: "Corpus", pattern: bytes, kinds: int, offset_base: int = 0, line_index_base: int = 0,
+             occ_capacity: int = 0) -> "Result":
+        opts = ScanOpts(offset_base, line_index_base, occ_capacity)
+        h = C.c_void_p()
+        _check(lib.xsg_scan(self._h, corpus._h, pattern, len(pattern), kinds, C.byref(opts), C.byref(h)))
+        return Result(h, kinds)
+
+    def search_host(self, buf, n_bytes: Optional[int], pattern: bytes, kinds: int,
+                    bounds: Optional[np.ndarray] = None, min_chunk: int = DEFAULT_MIN_CHUNK,
+                    offset_base: int = 0, line_index_base: int = 0) -> "Result":
+        """buf: numpy uint8 array or raw address (int) of a host buffer (pinned for full speed)."""
+        if isinstance(buf, np.ndarray):
+            addr, n = buf.ctypes.data, int(buf.size)
+        else:
+            addr, n = int(buf), int(n_bytes)
+        opts = ScanOpts(offset_base, line_index_base, 0)
+        h = C.c_void_p()
+        bp, nb = (None, 0) if bounds is None else (_u64ptr(bounds), int(bounds.size))
+        _check(lib.xsg_search_host(self._h, C.c_void_p(addr), n, bp, nb, min_chunk, pattern, len(pattern), kinds,
+                                   C.byref(opts), C.byref(h)))
+        return Result(h, kinds)
+
+
+class Corpus:
+    """Device-resident bytes + reference-chunk bounds (xsg_corpus)."""
+
+    def __init__(self, ctx: Context, handle, n: int):
+        self.ctx, self._h, self.size = ctx, handle, n
+
+    def free(self) -> None:
+        if self._h:
+            lib.xsg_corpus_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    @property
+    def device_ptr(self) -> int:
+        return lib.xsg_corpus_device_ptr(self._h) or 0
+
+    def upload(self, buf: np.ndarray, offset: int = 0) -> None:
+        _check(lib.xsg_corpus_upload(self._h, buf.ctypes.data, offset, int(buf.size)))
+
+    def download(self, offset: int = 0, n: Optional[int] = None) -> np.ndarray:
+        n = self.size - offset if n is None else n
+        out = np.empty(n, dtype=np.uint8)
+        _check(lib.xsg_corpus_download(self._h, out.ctypes.data, offset, n))
+        return out
+
+    def fill_synth(self, params: SynthParams, first_block: int = 0) -> None:
+        _check(lib.xsg_corpus_fill_synth(self._h, first_block, C.byref(params)))
+
+    def chunk(self, min_chunk: int = DEFAULT_MIN_CHUNK) -> None:
+        _check(lib.xsg_corpus_chunk(self._h, min_chunk))
+
+    def set_bounds(self, bounds: np.ndarray) -> None:
+        b = np.ascontiguousarray(bounds, dtype=np.uint64)
+        _check(lib.xsg_corpus_set_bounds(self._h, _u64ptr(b), int(b.size)))
+
+    def bounds(self) -> np.ndarray:
+        nb = lib.xsg_corpus_num_chunks(self._h)
+        out = np.empty(nb, dtype=np.uint64)
+        if nb:
+            _check(lib.xsg_corpus_get_bounds(self._h, _u64ptr(out), nb))
+        return out
+
+
+class Result:
+    """Device-resident result vectors of one search (xsg_result)."""
+
+    def __init__(self, handle, kinds: int):
+        self._h, self.kinds = handle, kinds
+
+    def free(self) -> None:
+        if self._h:
+            lib.xsg_result_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def count(self, kind: int) -> int:
+        return int(lib.xsg_result_count(self._h, kind))
+
+    def vector(self, kind: int) -> np.ndarray:
+        n = self.count(kind)
+        out = np.empty(n, dtype=np.uint64)
+        if n:
+            _check(lib.xsg_result_copy(self._h, kind, _u64ptr(out), n))
+        return out
+
+    def line_spans(self) -> Tuple[np.ndarray, np.ndarray]:
+        n = self.count(LINES)
+        st, ln = np.empty(n, dtype=np.uint64), np.empty(n, dtype=np.uint64)
+        if n:
+            _check(lib.xsg_result_copy(self._h, LINES, _u64ptr(st), n))
+            _check(lib.xsg_result_copy_line_lengths(self._h, _u64ptr(ln), n))
+        return st, ln
+
+    def device_ptr(self, kind: int) -> int:
+        return lib.xsg_result_device_ptr(self._h, kind) or 0
+
+    @property
+    def newlines(self) -> int:
+        return int(lib.xsg_result_newlines(self._h))
+
+    @property
+    def raw_occurrences(self) -> int:
+        return int(lib.xsg_result_raw_occurrences(self._h))
+
+    def timings(self) -> Timings:
+        t = Timings()
+        _check(lib.xsg_result_timings(self._h, C.byref(t)))
+        return t
+
+
+class _ResultView:
+    """What Searcher.get_result() hands out: size(), copy_result_safe(), blocking iteration."""
+
+    def __init__(self, searcher: "Searcher"):
+        self._s = searcher
+
+    def size(self) -> int:
+        self._s.join()
+        return self._s._size
+
+    def copy_result_safe(self):
+        self._s.join()
+        return list(self._s._values)
+
+    def __iter__(self) -> Iterator:
+        self._s.join()  # blocks until the producer closed the result (ResultTypes.h:48-60)
+        if self._s.kind in (COUNT, COUNT_LINES):
+            yield self._s._size  # running totals; the last value yielded is the total
+        else:
+            yield from self._s._values
+
+    def __len__(self) -> int:
+        return self.size()
+
+
+class Searcher:
+    """Mirror of xs::Searcher for this path: the search runs on a worker thread from construction."""
+
+    def __init__(self, kind: int, pattern: bytes, file_path: str, meta_file: Optional[str] = None,
+                 num_threads: int = 1, max_num_readers: int = 1, device: int = 0,
+                 min_chunk: int = DEFAULT_MIN_CHUNK):
+        if isinstance(pattern, str):
+            pattern = pattern.encode()
+        self.kind, self.pattern, self.file_path = kind, pattern, file_path
+        self._size, self._values, self._error = 0, [], None
+        self._device, self._min_chunk = device, min_chunk
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+
+    def _run(self) -> None:
+        try:
+            data = np.fromfile(self.file_path, dtype=np.uint8)
+            ctx = Context(self._device)
+            try:
+                res = ctx.search_host(data, None, self.pattern, self.kind, min_chunk=self._min_chunk)
+                self._size = res.count(self.kind)
+                if self.kind == LINES:
+                    st, ln = res.line_spans()
+                    raw = data.tobytes()
+                    self._values = [raw[int(s):int(s) + int(l)].decode("utf-8", "replace") for s, l in zip(st, ln)]
+                elif self.kind in _VECTOR_KINDS:
+                    self._values = [int(v) for v in res.vector(self.kind)]
+                res.free()
+            finally:
+                ctx.close()
+        except Exception as e:  # surfaced by join()
+            self._error = e
+
+    def join(self) -> None:
+        if self._thread.is_alive():
+            self._thread.join()
+        if self._error is not None:
+            raise self._error
+
+    def running(self) -> bool:
+        return self._thread.is_alive()
+
+    def get_result(self) -> _ResultView:
+        return _ResultView(self)
+
+    getResult = get_result
+
+
+def extern_search(tag, pattern, file_path: str, meta_file: Optional[str] = None, num_threads: int = 1,
+                  max_num_readers: int = 1, ignore_case: bool = False, **kw) -> Searcher:
+    """xs::extern_search<Tag>(pattern, file, meta_file, num_threads, max_num_readers)."""
+    kind = TAGS[tag] if isinstance(tag, str) else int(tag)
+    if ignore_case:
+        raise XsgError(-2, "ignore_case is not part of the GPU literal path")
+    return Searcher(kind, pattern, file_path, meta_file, num_threads, max_num_readers, **kw)
+
+
+def shard_exchange(newlines: int, counts: Sequence[int], group=None) -> Tuple[int, List[int], List[int]]:
+    """The one exchange step of the multi-GPU path: all-gather every shard's {newline count, result
+    counts}; returns (line-index base of this rank, output bases per count, global totals)."""
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return 0, [0 for _ in counts], [int(c) for c in counts]
+    backend = dist.get_backend(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    mine = torch.tensor([int(newlines)] + [int(c) for c in counts], dtype=torch.int64, device=dev)
+    world = dist.get_world_size(group)
+    allv = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allv, mine, group=group)
+    table = torch.stack(allv).cpu().numpy()
+    rank = dist.get_rank(group)
+    excl = table[:rank].sum(axis=0) if rank else np.zeros(table.shape[1], dtype=np.int64)
+    tot = table.sum(axis=0)
+    return int(excl[0]), [int(x) for x in excl[1:]], [int(x) for x in tot[1:]]

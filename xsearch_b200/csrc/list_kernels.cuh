@@ -1,0 +1,55 @@
+// list_kernels.cuh -- launchers of the small kernels around the byte scan (list_kernels.cu).
+#pragma once
+#include "xsg_common.cuh"
+
+namespace xsg {
+
+enum SelectMode : int {
+  kSelMatch = 0,          // xs::count / xs::match_byte_offsets, border-free pattern: every occurrence
+  kSelMatchBordered = 1,  // same tags, self-overlapping pattern: greedy leftmost non-overlapping
+  kSelLine = 2            // xs::count_lines / line_*: first occurrence of every line
+};
+
+// synthetic corpus: blocks [first_block, first_block + n_blocks) -> dst
+void launch_synth(uint8_t* dst, uint64_t first_block, uint64_t n_blocks, const xsg_synth_params& p, cudaStream_t s);
+
+// v1 chunker on the device: writes bounds (capacity cap) and *nb_out; one warp, sequential chunks
+void launch_chunker(const uint8_t* buf, uint64_t n, uint64_t min_chunk, uint64_t* bounds, uint64_t cap,
+                    unsigned long long* nb_out, cudaStream_t s);
+// *bad_out != 0 if bounds are not increasing / newline-aligned / do not end at n
+void launch_check_bounds(const uint8_t* buf, uint64_t n, const uint64_t* bounds, uint64_t nb, unsigned int* bad_out,
+                         cudaStream_t s);
+
+// sum of a u32 array into *out (out must be zero before)
+void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, cudaStream_t s);
+// exclusive scan u32 -> u64 (out[i] = sum in[0..i)), *total = sum; tmp holds div_up(n, 2048) u64
+void launch_exscan_u32(const uint32_t* in, uint64_t n, uint64_t* out, uint64_t* tmp, unsigned long long* total,
+                       cudaStream_t s);
+
+// selection flags of the non-zone part of every chunk
+void launch_select(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);
+// per-chunk: greedy resolution (bordered) and emulation of the reference's chunk tail; sets sel[]
+void launch_zone(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);
+// count-only variant without an occurrence list: adds to sub (true occurrences inside the tail zones)
+// and add (occurrences the reference reports there)
+void launch_zone_count(const uint8_t* buf, uint64_t n, const uint64_t* bounds, uint64_t nb, const Pattern& pat,
+                       const uint32_t* tile_count, unsigned long long* sub, unsigned long long* add, cudaStream_t s);
+
+struct CompactArgs {
+  ListArgs l;
+  uint64_t goff;               // global offset base
+  uint64_t lidx_base;          // line index base
+  const uint64_t* nl_prefix;   // [granules] exclusive '\n' prefix (line indices) or nullptr
+  uint64_t* out_match;         // any of these may be nullptr
+  uint64_t* out_line_off;
+  uint64_t* out_line_idx;
+  uint64_t* out_line_start;    // xs::lines: (start, len)
+  uint64_t* out_line_len;
+  unsigned long long* desc;    // [div_up(k, 2048)] zeroed look-back descriptors
+  unsigned int* ticket;        // zeroed
+  unsigned long long* total;   // number of selected entries
+  unsigned int* unterminated;  // set when the last selected line has no '\n' (xs::lines drops it)
+};
+void launch_compact(const CompactArgs& a, const Pattern& pat, cudaStream_t s);
+
+}  // namespace xsg

@@ -1,0 +1,251 @@
+// scan_kernel.cu -- the byte-scanning kernel (sm_100a): one pass over the corpus that
+//   * finds every true occurrence of the literal (exact SIMD-in-word compare for m <= 4, a two-byte
+//     SIMD filter + verification for m >= 5),
+//   * counts '\n' per 4 KiB granule (line-index accounting), and
+//   * either counts occurrences per tile or emits them, in file order, through a single-pass
+//     decoupled look-back scan (stream compaction).
+//
+// Replaces the inner loops of the reference: simd::strstr / strchr (simd_search.cpp:116-204) driven
+// by the findNext / findNextNewLine chains of search_wrappers.h:36-50,168-183,192-205.  The
+// sequential "next match -> skip -> next" chain is reformulated data-parallel: this kernel reports
+// ALL true occurrences; greedy non-overlap, first-hit-per-line and the reference's chunk-tail quirk
+// are resolved on the (much smaller) occurrence list by list_kernels.cu.
+//
+// Layout: a warp owns a 4 KiB granule (8 rows x 512 B), lane l holds bytes [16l,16l+16) of each row
+// => every load is one fully coalesced 16-byte ld.global.nc per thread, 8 independent loads in
+// flight per thread; the pattern-length halo is one extra 32-bit word per row obtained with a warp
+// shuffle (m <= 4 needs <= 3 halo bytes; the m >= 5 filter tests pattern bytes a and a+4).
+#include "xsg_common.cuh"
+
+namespace xsg {
+
+namespace {
+
+// keep only the lowest `valid` byte lanes (valid may be <= 0 or >= 4)
+__device__ __forceinline__ uint32_t keep_lanes(uint32_t w, long long valid) {
+  if (valid >= 4) return w;
+  if (valid <= 0) return 0u;
+  return w & ((1u << (8 * (int)valid)) - 1u);
+}
+
+// full compare of the pattern at corpus position q (slow path of the m >= 5 filter)
+__device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t q, const Pattern& pat) {
+  for (uint32_t k = 0; k < pat.m; ++k)
+    if (buf[q + k] != pat.bytes[k]) return false;
+  return true;
+}
+
+// NS: 1..4 = exact compare of m = NS consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verify
+template <int NS, bool EMIT, bool NL>
+__global__ void __launch_bounds__(kThreads, EMIT ? 2 : 3)
+scan_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  __shared__ uint32_t s_warp_cnt[kWarps];
+  __shared__ unsigned long long s_tile_base;
+  __shared__ unsigned int s_tile;
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+
+  uint64_t tile;
+  if (EMIT) {
+    if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    tile = s_tile;
+  } else {
+    tile = blockIdx.x;
+  }
+  const uint64_t tile_off = tile * (uint64_t)kTileBytes;
+  const uint64_t gran_off = tile_off + (uint64_t)warp * kGranuleBytes;
+  const uint64_t lane_off = gran_off + (uint64_t)lane * 16;
+  const bool partial = tile_off + kTileBytes + 16 > a.n;
+  const uint8_t* __restrict__ buf = a.buf;
+  const uint64_t n = a.n;
+
+  // ---- load the granule: 8 independent coalesced 16-byte loads per thread -------------------
+  uint4 v[kRows];
+  uint32_t ext = 0;  // lane 0: first word behind the granule (halo of the last row)
+  if (!partial) {
+#pragma unroll
+    for (int u = 0; u < kRows; ++u) v[u] = ld_stream_v4(reinterpret_cast<const uint4*>(buf + lane_off + u * kRowBytes));
+    if (lane == 0) ext = __ldg(reinterpret_cast<const uint32_t*>(buf + gran_off + kGranuleBytes));
+  } else {
+#pragma unroll
+    for (int u = 0; u < kRows; ++u) {
+      const uint64_t pos = lane_off + u * kRowBytes;
+      uint4 t = make_uint4(0, 0, 0, 0);
+      if (pos < n) {
+        t = ld_stream_v4(reinterpret_cast<const uint4*>(buf + pos));
+        const long long valid = (long long)(n - pos);
+        t.x = keep_lanes(t.x, valid);
+        t.y = keep_lanes(t.y, valid - 4);
+        t.z = keep_lanes(t.z, valid - 8);
+        t.w = keep_lanes(t.w, valid - 12);
+      }
+      v[u] = t;
+    }
+    if (lane == 0) {
+      const uint64_t pos = gran_off + kGranuleBytes;
+      if (pos < n) ext = keep_lanes(__ldg(reinterpret_cast<const uint32_t*>(buf + pos)), (long long)(n - pos));
+    }
+  }
+
+  uint32_t flags[EMIT ? kRows : 1][4];
+  uint32_t cnt = 0;    // occurrences owned by this lane
+  uint32_t nonnl = 0;  // bytes that are not '\n' (zero padding included)
+  const long long last_q = (long long)n - (long long)pat.m;  // last valid occurrence start
+
+#pragma unroll
+  for (int u = 0; u < kRows; ++u) {
+    const uint32_t w0 = v[u].x, w1 = v[u].y, w2 = v[u].z, w3 = v[u].w;
+    // halo word: lane l takes word 0 of lane l+1; lane 31 takes word 0 of the next row (held by lane 0)
+    uint32_t send = w0;
+    if (lane == 0) send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
+    const uint32_t w4 = __shfl_sync(kFull, send, (lane + 1) & 31);
+    const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
+
+    if (NL) {
+      nonnl += __popc(nonzero_lanes(w0 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w1 ^ 0x0a0a0a0au)) +
+               __popc(nonzero_lanes(w2 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w3 ^ 0x0a0a0a0au));
+    }
+
+    uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
+    if (NS <= 4) {
+      uint32_t z0 = w0 ^ pat.rep[0], z1 = w1 ^ pat.rep[0], z2 = w2 ^ pat.rep[0], z3 = w3 ^ pat.rep[0];
+#pragma unroll
+      for (int k = 1; k < NS; ++k) {  // byte k of the window: data shifted down by k bytes
+        z0 |= __funnelshift_r(w0, w1, 8 * k) ^ pat.rep[k];
+        z1 |= __funnelshift_r(w1, w2, 8 * k) ^ pat.rep[k];
+        z2 |= __funnelshift_r(w2, w3, 8 * k) ^ pat.rep[k];
+        z3 |= __funnelshift_r(w3, w4, 8 * k) ^ pat.rep[k];
+      }
+      f0 = zero_lanes(z0);
+      f1 = zero_lanes(z1);
+      f2 = zero_lanes(z2);
+      f3 = zero_lanes(z3);
+      if (partial) {  // zero padding / bytes behind n must not match
+        const long long lim = last_q + 1 - (long long)pos0;
+        f0 = keep_lanes(f0, lim);
+        f1 = keep_lanes(f1, lim - 4);
+        f2 = keep_lanes(f2, lim - 8);
+        f3 = keep_lanes(f3, lim - 12);
+      }
+      if (!EMIT) cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+    } else {
+      // filter: pattern byte a at this position AND pattern byte a+4 one word further
+      const uint32_t z0 = (w0 ^ pat.rep[0]) | (w1 ^ pat.rep[1]);
+      const uint32_t z1 = (w1 ^ pat.rep[0]) | (w2 ^ pat.rep[1]);
+      const uint32_t z2 = (w2 ^ pat.rep[0]) | (w3 ^ pat.rep[1]);
+      const uint32_t z3 = (w3 ^ pat.rep[0]) | (w4 ^ pat.rep[1]);
+      const uint32_t any = (haszero_filter(z0) | haszero_filter(z1) | haszero_filter(z2) | haszero_filter(z3)) & k80;
+      if (__any_sync(kFull, any != 0)) {
+        if (any != 0) {
+          uint32_t e[4] = {zero_lanes(z0), zero_lanes(z1), zero_lanes(z2), zero_lanes(z3)};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t word = e[j], keep = 0;
+            while (word) {
+              const int bit = __ffs(word) - 1;  // 7, 15, 23 or 31
+              word &= word - 1;
+              const long long q = (long long)(pos0 + 4 * j + (bit >> 3)) - (long long)pat.anchor;
+              if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) keep |= 1u << bit;
+            }
+            e[j] = keep;
+          }
+          f0 = e[0]; f1 = e[1]; f2 = e[2]; f3 = e[3];
+          if (!EMIT) cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+        }
+      }
+    }
+    if (EMIT) {
+      flags[u][0] = f0; flags[u][1] = f1; flags[u][2] = f2; flags[u][3] = f3;
+      cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+    }
+  }
+
+  // ---- granule / tile aggregates -----------------------------------------------------------
+  if (NL) {
+    const uint32_t s = warp_sum(nonnl);
+    if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
+  }
+  const uint32_t wcnt = warp_sum(cnt);
+  if (lane == 0) s_warp_cnt[warp] = wcnt;
+  __syncthreads();
+
+  if (!EMIT) {
+    if (threadIdx.x == 0) {
+      uint32_t t = 0;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
+      a.tile_count[tile] = t;
+    }
+    return;
+  }
+
+  // ---- emit mode: ordered stream compaction ---------------------------------------------------
+  if (warp == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
+    const unsigned long long excl = lookback(a.desc, tile, t, lane);
+    if (lane == 0) {
+      s_tile_base = excl;
+      a.tile_count[tile] = t;
+    }
+  }
+  __syncthreads();
+  if (wcnt == 0) return;  // warp-uniform
+  unsigned long long base = s_tile_base;
+  for (int w = 0; w < warp; ++w) base += s_warp_cnt[w];
+
+#pragma unroll
+  for (int u = 0; u < (EMIT ? kRows : 1); ++u) {
+    const uint32_t c = __popc(flags[u][0]) + __popc(flags[u][1]) + __popc(flags[u][2]) + __popc(flags[u][3]);
+    if (!__any_sync(kFull, c != 0)) continue;
+    uint32_t inc = c;  // inclusive warp scan of the per-lane counts of this row
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(kFull, inc, o);
+      if (lane >= o) inc += t;
+    }
+    unsigned long long slot = base + (inc - c);
+    base += __shfl_sync(kFull, inc, 31);
+    const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes - pat.anchor;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t word = flags[u][j];
+      while (word) {
+        const int bit = __ffs(word) - 1;
+        word &= word - 1;
+        if (slot < a.occ_cap) a.occ[slot] = pos0 + 4 * j + (bit >> 3);
+        ++slot;
+      }
+    }
+  }
+}
+
+template <int NS>
+void launch_ns(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, cudaStream_t s) {
+  const dim3 grid((unsigned)a.n_tiles), block(kThreads);
+  if (emit) {
+    if (newlines) scan_kernel<NS, true, true><<<grid, block, 0, s>>>(pat, a);
+    else scan_kernel<NS, true, false><<<grid, block, 0, s>>>(pat, a);
+  } else {
+    if (newlines) scan_kernel<NS, false, true><<<grid, block, 0, s>>>(pat, a);
+    else scan_kernel<NS, false, false><<<grid, block, 0, s>>>(pat, a);
+  }
+}
+
+}  // namespace
+
+void launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, cudaStream_t s) {
+  if (a.n_tiles == 0) return;
+  switch (pat.m) {
+    case 1: launch_ns<1>(pat, a, emit, newlines, s); break;
+    case 2: launch_ns<2>(pat, a, emit, newlines, s); break;
+    case 3: launch_ns<3>(pat, a, emit, newlines, s); break;
+    case 4: launch_ns<4>(pat, a, emit, newlines, s); break;
+    default: launch_ns<5>(pat, a, emit, newlines, s); break;
+  }
+}
+
+}  // namespace xsg

@@ -1,0 +1,145 @@
+// xsg_common.cuh -- shared declarations of the sm_100a scan-and-match kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/xsg.h"
+
+namespace xsg {
+
+// ---- geometry of the byte-scanning kernel -------------------------------------------------
+// A warp owns a contiguous "granule" of ROWS rows x 512 B; lane l holds bytes [16l, 16l+16) of
+// every row (one coalesced 16-byte load per row).  A CTA (tile) is WARPS consecutive granules.
+constexpr int kRows = 8;                          // rows per warp granule
+constexpr int kWarps = 8;                         // warps per CTA
+constexpr int kThreads = kWarps * 32;
+constexpr uint32_t kRowBytes = 512;               // 32 lanes x 16 B
+constexpr uint32_t kGranuleBytes = kRows * kRowBytes;       // 4 KiB: granularity of the newline table
+constexpr uint32_t kTileBytes = kWarps * kGranuleBytes;     // 32 KiB per CTA
+
+// ---- pattern descriptor handed to every kernel (lives in the constant bank) ----------------
+struct Pattern {
+  uint8_t bytes[XSG_MAX_PATTERN];
+  uint32_t m;        // pattern length
+  uint32_t nsimd;    // bytes tested SIMD-in-word: m for m <= 4 (exact), 2 for m >= 5 (filter)
+  uint32_t anchor;   // m >= 5: pattern index a of the first filter byte (second is a + 4)
+  uint32_t rep[4];   // the SIMD-tested bytes replicated into all four lanes of a word
+  uint32_t bordered; // pattern overlaps itself (has a proper border) -> greedy resolution needed
+};
+
+// ---- scan kernel launch arguments ---------------------------------------------------------
+struct ScanArgs {
+  const uint8_t* buf;     // corpus bytes, 16-byte aligned
+  uint64_t n;             // corpus size in bytes
+  uint64_t n_tiles;
+  uint32_t* tile_count;   // [n_tiles] occurrences owned by each tile (ownership by anchor byte)
+  uint32_t* nl_granule;   // [n_tiles * kWarps] '\n' per 4 KiB granule (newline mode) or nullptr
+  uint64_t* occ;          // raw occurrence list (emit mode) or nullptr
+  uint64_t occ_cap;
+  unsigned long long* desc;    // [n_tiles] decoupled look-back descriptors (emit mode)
+  unsigned int* ticket;        // dynamic tile id (emit mode)
+};
+
+// launchers implemented in scan_kernel.cu
+void launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, cudaStream_t s);
+
+// ---- list-domain (post) kernels, list_kernels.cu -------------------------------------------
+struct ListArgs {
+  const uint8_t* buf;
+  uint64_t n;
+  const uint64_t* bounds;  // device: exclusive chunk ends
+  uint64_t nb;
+  const uint64_t* occ;     // sorted raw occurrences
+  uint64_t k;              // number of raw occurrences
+  uint8_t* sel;            // [k] selection flags (output of select / zone kernels)
+};
+
+// small helpers usable from host code
+inline uint64_t div_up(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+// ---- device helpers -------------------------------------------------------------------------
+#if defined(__CUDACC__)
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// streaming 16-byte load: read-only path, do not allocate in L1 (each byte is read once)
+__device__ __forceinline__ uint4 ld_stream_v4(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+constexpr uint32_t k7F = 0x7f7f7f7fu;
+constexpr uint32_t k80 = 0x80808080u;
+constexpr uint32_t k01 = 0x01010101u;
+
+// exact per-lane zero test: 0x80 in every byte lane of z that is zero (3 instructions)
+__device__ __forceinline__ uint32_t zero_lanes(uint32_t z) {
+  uint32_t b = (z & k7F) + k7F;
+  return ~(b | z) & k80;
+}
+// exact per-lane non-zero test: 0x80 in every byte lane of z that is NOT zero
+__device__ __forceinline__ uint32_t nonzero_lanes(uint32_t z) {
+  uint32_t b = (z & k7F) + k7F;
+  return (b | z) & k80;
+}
+// word-level "has a zero byte" predicate (non-zero result <=> some lane is zero); lanes above the
+// lowest zero lane may carry false flags, so use it only as a filter (2 instructions)
+__device__ __forceinline__ uint32_t haszero_filter(uint32_t z) { return (z - k01) & ~z; }
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr unsigned long long kStatusShift = 62;
+constexpr unsigned long long kAggregate = 1ull << kStatusShift;
+constexpr unsigned long long kPrefix = 2ull << kStatusShift;
+constexpr unsigned long long kValueMask = (1ull << kStatusShift) - 1;
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(kFull, v); }
+
+
+// Decoupled look-back (Merrill & Garland): returns the exclusive prefix of `aggregate` over all
+// tiles before `tile`; called by warp 0 only.  desc[] was zeroed before the launch; tile ids are
+// handed out by a ticket so every predecessor is resident or finished (forward progress).
+__device__ __forceinline__ unsigned long long lookback(unsigned long long* desc, uint64_t tile,
+                                                       unsigned long long aggregate, int lane) {
+  if (tile == 0) {
+    if (lane == 0) st_relaxed_u64(&desc[0], kPrefix | aggregate);
+    return 0;
+  }
+  if (lane == 0) st_relaxed_u64(&desc[tile], kAggregate | aggregate);
+  unsigned long long excl = 0;
+  long long idx = (long long)tile - 1;
+  while (true) {
+    long long my = idx - lane;
+    unsigned long long d;
+    unsigned st;
+    do {
+      d = my >= 0 ? ld_relaxed_u64(&desc[my]) : kPrefix;  // virtual tile -1: prefix 0
+      st = (unsigned)(d >> kStatusShift);
+    } while (__any_sync(kFull, st == 0));
+    unsigned pm = __ballot_sync(kFull, st == 2);
+    unsigned long long val = d & kValueMask;
+    if (pm) {
+      int first = __ffs(pm) - 1;  // nearest predecessor holding an inclusive prefix
+      if (lane > first) val = 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(kFull, val, o);
+    excl += val;
+    if (pm) break;
+    idx -= 32;
+  }
+  if (lane == 0) st_relaxed_u64(&desc[tile], kPrefix | (excl + aggregate));
+  return excl;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace xsg

@@ -1,0 +1,89 @@
+// xsg_internal.h -- host-side objects behind the opaque handles of include/xsg.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "list_kernels.cuh"
+#include "xsg_common.cuh"
+
+namespace xsg {
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define XSG_CUDA(expr)                                                    \
+  do {                                                                    \
+    cudaError_t e__ = (expr);                                             \
+    if (e__ != cudaSuccess) return xsg::cuda_fail(e__, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+// grow-only device scratch buffer
+struct Scratch {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes);  // returns XSG_OK / XSG_ERR_NOMEM; contents are NOT preserved
+  void release();
+  template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+// device scalars of one scan (zeroed at the start, read back through a pinned mirror)
+struct DevScalars {
+  unsigned long long nl_total;
+  unsigned long long occ_total;
+  unsigned long long zone_sub, zone_add;
+  unsigned long long sel_total[2];  // [0] match family, [1] line family
+  unsigned long long nb_out;
+  unsigned int unterminated;
+  unsigned int bad_bounds;
+  unsigned int ticket[4];
+  unsigned int pad[2];
+};
+
+}  // namespace xsg
+
+struct xsg_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;       // compute
+  cudaStream_t copy_stream = nullptr;  // H2D of streamed segments
+  cudaEvent_t ev[6] = {};
+  xsg::Scratch tile_count, nl_granule, nl_prefix, scan_tmp, desc, occ, sel, desc2;
+  xsg::Scratch stage[2];               // streamed segments (double buffer)
+  xsg::Scratch seg_bounds;
+  cudaEvent_t stage_copied[2] = {}, stage_free[2] = {};
+  xsg::DevScalars* d_scalars = nullptr;
+  xsg::DevScalars* h_scalars = nullptr;  // pinned
+};
+
+struct xsg_corpus {
+  xsg_ctx* ctx = nullptr;
+  uint8_t* dev = nullptr;
+  uint64_t n = 0;
+  bool owned = false;
+  uint64_t* d_bounds = nullptr;
+  std::vector<uint64_t> h_bounds;
+};
+
+struct xsg_part {  // results of one device-resident scan (one streamed segment)
+  uint64_t* match_off = nullptr;
+  uint64_t* line_off = nullptr;
+  uint64_t* line_idx = nullptr;
+  uint64_t* line_start = nullptr;
+  uint64_t* line_len = nullptr;
+  uint64_t n_match = 0;  // entries in match_off / value of xs::count
+  uint64_t n_line = 0;   // entries in line_off / line_idx / value of xs::count_lines
+  uint64_t n_lines = 0;  // entries in line_start / line_len (xs::lines; may be n_line - 1)
+};
+
+struct xsg_result {
+  xsg_ctx* ctx = nullptr;
+  uint32_t kinds = 0;
+  std::vector<xsg_part> parts;
+  uint64_t count = 0, count_lines = 0, n_lines = 0;
+  uint64_t newlines = 0, raw_occurrences = 0;
+  xsg_timings timings = {};
+  // lazily concatenated device copies for xsg_result_device_ptr on multi-part results
+  uint64_t* concat[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+};

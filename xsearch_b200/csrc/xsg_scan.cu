@@ -1,0 +1,273 @@
+// xsg_scan.cu -- the scan pipeline behind xsg_scan / xsg_search_host and the result accessors.
+//
+// Stages (the reference's chunk -> search -> result loop, Searcher.h:100-120, as stream-ordered
+// kernel launches):
+//   A  scan_kernel      : every byte once; all true occurrences (+ '\n' per 4 KiB granule)
+//   B  select / zone    : reference semantics on the occurrence list (greedy, per-line, chunk tail)
+//   C  compact          : stable compaction + formatting of the requested result vectors
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "xsg_internal.h"
+
+using namespace xsg;
+
+namespace {
+
+constexpr uint32_t kMatchKinds = XSG_COUNT | XSG_MATCH_BYTE_OFFSETS;
+constexpr uint32_t kLineKinds = XSG_COUNT_LINES | XSG_LINE_BYTE_OFFSETS | XSG_LINE_INDICES | XSG_LINES;
+constexpr uint32_t kAllKinds = kMatchKinds | kLineKinds;
+
+// rough byte frequencies of English text; only used to pick the two filter bytes of a long pattern
+uint32_t byte_weight(uint8_t c) {
+  static const uint8_t lower[26] = {65, 12, 23, 35, 100, 18, 16, 50, 57, 1, 6, 33, 20,
+                                    57, 62, 15, 1, 50, 52, 75, 23, 8, 19, 1, 16, 1};
+  if (c == ' ') return 180;
+  if (c >= 'a' && c <= 'z') return lower[c - 'a'];
+  if (c >= 'A' && c <= 'Z') return lower[c - 'A'] / 15 + 1;
+  if (c == '\n') return 30;
+  if (c == '.' || c == ',') return 10;
+  if (c >= '0' && c <= '9') return 3;
+  return 1;
+}
+
+int make_pattern(const uint8_t* p, uint32_t m, Pattern* out) {
+  if (!p || m == 0 || m > XSG_MAX_PATTERN) {
+    set_error("pattern length must be 1..64");
+    return XSG_ERR_ARG;
+  }
+  for (uint32_t i = 0; i < m; ++i)
+    if (p[i] == '\n') {
+      set_error("the pattern must not contain '\\n'");
+      return XSG_ERR_ARG;
+    }
+  Pattern pat;
+  std::memset(&pat, 0, sizeof pat);
+  std::memcpy(pat.bytes, p, m);
+  pat.m = m;
+  auto rep = [](uint8_t c) { return 0x01010101u * c; };
+  if (m <= 4) {
+    pat.nsimd = m;
+    for (uint32_t i = 0; i < m; ++i) pat.rep[i] = rep(p[i]);
+  } else {
+    pat.nsimd = 2;
+    uint32_t best = 0, best_w = ~0u;
+    for (uint32_t a = 0; a + 4 < m; ++a) {
+      const uint32_t w = byte_weight(p[a]) * byte_weight(p[a + 4]);
+      if (w < best_w) { best_w = w; best = a; }
+    }
+    pat.anchor = best;
+    pat.rep[0] = rep(p[best]);
+    pat.rep[1] = rep(p[best + 4]);
+  }
+  // bordered <=> the KMP failure value of the whole pattern is > 0
+  uint32_t fail[XSG_MAX_PATTERN + 1];
+  fail[0] = 0;
+  if (m > 1) {
+    fail[1] = 0;
+    uint32_t k = 0;
+    for (uint32_t i = 1; i < m; ++i) {
+      while (k > 0 && p[i] != p[k]) k = fail[k];
+      if (p[i] == p[k]) ++k;
+      fail[i + 1] = k;
+    }
+    pat.bordered = fail[m] > 0;
+  }
+  *out = pat;
+  return XSG_OK;
+}
+
+void free_part(xsg_ctx* ctx, xsg_part& p) {
+  uint64_t** arrs[] = {&p.match_off, &p.line_off, &p.line_idx, &p.line_start, &p.line_len};
+  for (uint64_t** a : arrs) {
+    if (*a) cudaFreeAsync(*a, ctx->stream);
+    *a = nullptr;
+  }
+}
+
+int alloc_out(xsg_ctx* ctx, uint64_t** p, uint64_t entries) {
+  *p = nullptr;
+  XSG_CUDA(cudaMallocAsync(p, std::max<uint64_t>(entries, 1) * sizeof(uint64_t), ctx->stream));
+  return XSG_OK;
+}
+
+struct ScanStats {
+  uint64_t newlines = 0, raw = 0;
+  float main_ms = 0, post_ms = 0, scan_ms = 0;
+  uint32_t launches = 0;
+};
+
+int read_scalars(xsg_ctx* ctx) {
+  XSG_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(DevScalars), cudaMemcpyDeviceToHost, ctx->stream));
+  XSG_CUDA(cudaStreamSynchronize(ctx->stream));
+  return XSG_OK;
+}
+
+// One device-resident scan of buf[0..n) with reference chunks d_bounds[0..nb).
+int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_bounds, uint64_t nb,
+                const Pattern& pat, uint32_t kinds, uint64_t goff, uint64_t lidx_base, uint64_t occ_cap_opt,
+                xsg_part* part, ScanStats* st) {
+  cudaStream_t s = ctx->stream;
+  *part = xsg_part();
+  XSG_CUDA(cudaEventRecord(ctx->ev[0], s));
+  XSG_CUDA(cudaMemsetAsync(ctx->d_scalars, 0, sizeof(DevScalars), s));
+  if (n == 0 || nb == 0) {
+    XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
+    XSG_CUDA(cudaStreamSynchronize(s));
+    return XSG_OK;
+  }
+  const bool want_match = (kinds & kMatchKinds) != 0, want_line = (kinds & kLineKinds) != 0;
+  const bool want_idx = (kinds & XSG_LINE_INDICES) != 0;
+  // xs::count alone with a pattern that cannot overlap itself needs no occurrence list
+  const bool count_only = kinds == XSG_COUNT && !pat.bordered;
+  const uint64_t n_tiles = div_up(n, kTileBytes);
+  int rc;
+  if ((rc = ctx->tile_count.reserve(n_tiles * sizeof(uint32_t)))) return rc;
+  ScanArgs a{};
+  a.buf = buf;
+  a.n = n;
+  a.n_tiles = n_tiles;
+  a.tile_count = ctx->tile_count.as<uint32_t>();
+  DevScalars* ds = ctx->d_scalars;
+
+  if (count_only) {
+    XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
+    launch_scan(pat, a, false, false, s);
+    XSG_CUDA(cudaGetLastError());
+    XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
+    launch_reduce_u32(a.tile_count, n_tiles, &ds->occ_total, s);
+    launch_zone_count(buf, n, d_bounds, nb, pat, a.tile_count, &ds->zone_sub, &ds->zone_add, s);
+    XSG_CUDA(cudaGetLastError());
+    st->launches += 2 + (pat.m > 1 ? 1 : 0);
+    XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
+    if ((rc = read_scalars(ctx))) return rc;
+    const DevScalars& h = *ctx->h_scalars;
+    st->raw += h.occ_total;
+    part->n_match = h.occ_total - h.zone_sub + h.zone_add;
+  } else {
+    if ((rc = ctx->desc.reserve(n_tiles * sizeof(unsigned long long)))) return rc;
+    if (want_idx) {
+      const uint64_t n_gran = n_tiles * kWarps;
+      if ((rc = ctx->nl_granule.reserve(n_gran * sizeof(uint32_t)))) return rc;
+      if ((rc = ctx->nl_prefix.reserve((n_gran + 1) * sizeof(uint64_t)))) return rc;
+      if ((rc = ctx->scan_tmp.reserve((div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
+      a.nl_granule = ctx->nl_granule.as<uint32_t>();
+    }
+    a.desc = ctx->desc.as<unsigned long long>();
+    a.ticket = &ds->ticket[0];
+    uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
+    uint64_t k = 0;
+    for (int attempt = 0;; ++attempt) {
+      if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
+      a.occ = ctx->occ.as<uint64_t>();
+      a.occ_cap = cap;
+      XSG_CUDA(cudaMemsetAsync(a.desc, 0, n_tiles * sizeof(unsigned long long), s));
+      XSG_CUDA(cudaMemsetAsync(&ds->ticket[0], 0, sizeof(unsigned int), s));
+      XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
+      launch_scan(pat, a, true, want_idx, s);
+      XSG_CUDA(cudaGetLastError());
+      XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
+      st->launches += 1;
+      unsigned long long last = 0;
+      XSG_CUDA(cudaMemcpyAsync(&last, a.desc + (n_tiles - 1), sizeof last, cudaMemcpyDeviceToHost, s));
+      XSG_CUDA(cudaStreamSynchronize(s));
+      k = last & ((1ull << 62) - 1);
+      if (k <= cap) break;
+      if (attempt > 0) {
+        set_error("occurrence buffer overflow after retry");
+        return XSG_ERR_STATE;
+      }
+      cap = k;  // rare: denser than the estimate -> rescan with the exact capacity
+    }
+    st->raw += k;
+    if (want_idx) {
+      launch_exscan_u32(a.nl_granule, n_tiles * kWarps, ctx->nl_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
+                        &ds->nl_total, s);
+      st->launches += 3;
+    }
+    if (k > 0) {
+      if ((rc = ctx->sel.reserve(k))) return rc;
+      const uint64_t n_ct = div_up(k, 2048);
+      if ((rc = ctx->desc2.reserve(n_ct * sizeof(unsigned long long)))) return rc;
+      ListArgs l{buf, n, d_bounds, nb, ctx->occ.as<uint64_t>(), k, ctx->sel.as<uint8_t>()};
+      for (int fam = 0; fam < 2; ++fam) {
+        if (fam == 0 ? !want_match : !want_line) continue;
+        const int mode = fam == 1 ? kSelLine : (pat.bordered ? kSelMatchBordered : kSelMatch);
+        launch_select(l, pat, mode, s);
+        launch_zone(l, pat, mode, s);
+        st->launches += 1 + (pat.m > 1 ? 1 : 0);
+        CompactArgs c{};
+        c.l = l;
+        c.goff = goff;
+        c.lidx_base = lidx_base;
+        c.nl_prefix = ctx->nl_prefix.as<uint64_t>();
+        if (fam == 0) {
+          if (kinds & XSG_MATCH_BYTE_OFFSETS) {
+            if ((rc = alloc_out(ctx, &part->match_off, k))) return rc;
+            c.out_match = part->match_off;
+          }
+        } else {
+          if (kinds & XSG_LINE_BYTE_OFFSETS) {
+            if ((rc = alloc_out(ctx, &part->line_off, k))) return rc;
+            c.out_line_off = part->line_off;
+          }
+          if (kinds & XSG_LINE_INDICES) {
+            if ((rc = alloc_out(ctx, &part->line_idx, k))) return rc;
+            c.out_line_idx = part->line_idx;
+          }
+          if (kinds & XSG_LINES) {
+            if ((rc = alloc_out(ctx, &part->line_start, k))) return rc;
+            if ((rc = alloc_out(ctx, &part->line_len, k))) return rc;
+            c.out_line_start = part->line_start;
+            c.out_line_len = part->line_len;
+          }
+        }
+        c.desc = ctx->desc2.as<unsigned long long>();
+        c.ticket = &ds->ticket[1 + fam];
+        c.total = &ds->sel_total[fam];
+        c.unterminated = &ds->unterminated;
+        XSG_CUDA(cudaMemsetAsync(c.desc, 0, n_ct * sizeof(unsigned long long), s));
+        launch_compact(c, pat, s);
+        XSG_CUDA(cudaGetLastError());
+        st->launches += 1;
+      }
+    }
+    XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
+    if ((rc = read_scalars(ctx))) return rc;
+    const DevScalars& h = *ctx->h_scalars;
+    part->n_match = h.sel_total[0];
+    part->n_line = h.sel_total[1];
+    part->n_lines = (kinds & XSG_LINES) ? h.sel_total[1] - (h.unterminated ? 1 : 0) : 0;
+    st->newlines += h.nl_total;
+  }
+  float ms = 0;
+  XSG_CUDA(cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]));
+  st->main_ms += ms;
+  XSG_CUDA(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]));
+  st->post_ms += ms;
+  XSG_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]));
+  st->scan_ms += ms;
+  return XSG_OK;
+}
+
+void finish_result(xsg_result* r, const ScanStats& st) {
+  for (const xsg_part& p : r->parts) {
+    r->count += p.n_match;
+    r->count_lines += p.n_line;
+    r->n_lines += p.n_lines;
+  }
+  r->newlines = st.newlines;
+  r->raw_occurrences = st.raw;
+  r->timings.scan_ms = st.scan_ms;
+  r->timings.main_kernel_ms = st.main_ms;
+  r->timings.post_ms = st.post_ms;
+  r->timings.kernel_launches = st.launches;
+}
+
+}  // namespace
+
+#include "xsg_scan_api.inc"
