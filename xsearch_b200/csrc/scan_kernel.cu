@@ -15,6 +15,11 @@
 // => every load is one fully coalesced 16-byte ld.global.nc per thread, 8 independent loads in
 // flight per thread; the pattern-length halo is one extra 32-bit word per row obtained with a warp
 // shuffle (m <= 4 needs <= 3 halo bytes; the m >= 5 filter tests pattern bytes a and a+4).
+//
+// Emit mode is a persistent kernel: CTAs draw tile ids from a ticket counter (the next ticket is
+// fetched while the current tile is processed), keep the per-lane occurrence masks as 16 bits per
+// row (4 registers per thread) across the look-back, and tiles without occurrences publish their
+// aggregate and skip the look-back altogether.
 #include "xsg_common.cuh"
 
 namespace xsg {
@@ -35,31 +40,23 @@ __device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t
   return true;
 }
 
-// NS: 1..4 = exact compare of m = NS consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verify
+// flags at bits 7/15/23/31 of f -> 4 bits in lane order
+__device__ __forceinline__ uint32_t nibble_of(uint32_t f) { return (f * 0x00204081u) >> 28; }
+
+struct LaneResult {
+  uint32_t mask[kRows / 2];  // EMIT: 16 occurrence bits per row, two rows per register
+  uint32_t cnt;              // occurrences owned by this lane
+  uint32_t nonnl;            // bytes that are not '\n' (zero padding included)
+};
+
+// Phase 1 for one warp granule: load, classify, (verify), count.  NS: 1..4 = exact compare of m = NS
+// consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification.
 template <int NS, bool EMIT, bool NL>
-__global__ void __launch_bounds__(kThreads, EMIT ? 2 : 3)
-scan_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
-  __shared__ uint32_t s_warp_cnt[kWarps];
-  __shared__ unsigned long long s_tile_base;
-  __shared__ unsigned int s_tile;
-
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-
-  uint64_t tile;
-  if (EMIT) {
-    if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
-    __syncthreads();
-    tile = s_tile;
-  } else {
-    tile = blockIdx.x;
-  }
-  const uint64_t tile_off = tile * (uint64_t)kTileBytes;
+__device__ __forceinline__ void scan_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
+                                             uint64_t tile_off, int warp, int lane, LaneResult& r) {
   const uint64_t gran_off = tile_off + (uint64_t)warp * kGranuleBytes;
   const uint64_t lane_off = gran_off + (uint64_t)lane * 16;
-  const bool partial = tile_off + kTileBytes + 16 > a.n;
-  const uint8_t* __restrict__ buf = a.buf;
-  const uint64_t n = a.n;
+  const bool partial = tile_off + kTileBytes + 16 > n;
 
   // ---- load the granule: 8 independent coalesced 16-byte loads per thread -------------------
   uint4 v[kRows];
@@ -89,9 +86,10 @@ scan_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
     }
   }
 
-  uint32_t flags[EMIT ? kRows : 1][4];
-  uint32_t cnt = 0;    // occurrences owned by this lane
-  uint32_t nonnl = 0;  // bytes that are not '\n' (zero padding included)
+  r.cnt = 0;
+  r.nonnl = 0;
+#pragma unroll
+  for (int i = 0; i < kRows / 2; ++i) r.mask[i] = 0;
   const long long last_q = (long long)n - (long long)pat.m;  // last valid occurrence start
 
 #pragma unroll
@@ -104,8 +102,8 @@ scan_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
     if (NL) {
-      nonnl += __popc(nonzero_lanes(w0 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w1 ^ 0x0a0a0a0au)) +
-               __popc(nonzero_lanes(w2 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w3 ^ 0x0a0a0a0au));
+      r.nonnl += __popc(nonzero_lanes(w0 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w1 ^ 0x0a0a0a0au)) +
+                 __popc(nonzero_lanes(w2 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w3 ^ 0x0a0a0a0au));
     }
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
@@ -129,7 +127,11 @@ scan_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
         f2 = keep_lanes(f2, lim - 8);
         f3 = keep_lanes(f3, lim - 12);
       }
-      if (!EMIT) cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+      r.cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+      if (EMIT && (f0 | f1 | f2 | f3)) {
+        const uint32_t m16 = nibble_of(f0) | (nibble_of(f1) << 4) | (nibble_of(f2) << 8) | (nibble_of(f3) << 12);
+        r.mask[u >> 1] |= m16 << (16 * (u & 1));
+      }
     } else {
       // filter: pattern byte a at this position AND pattern byte a+4 one word further
       const uint32_t z0 = (w0 ^ pat.rep[0]) | (w1 ^ pat.rep[1]);
@@ -139,112 +141,160 @@ scan_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
       const uint32_t any = (haszero_filter(z0) | haszero_filter(z1) | haszero_filter(z2) | haszero_filter(z3)) & k80;
       if (__any_sync(kFull, any != 0)) {
         if (any != 0) {
-          uint32_t e[4] = {zero_lanes(z0), zero_lanes(z1), zero_lanes(z2), zero_lanes(z3)};
+          const uint32_t e[4] = {zero_lanes(z0), zero_lanes(z1), zero_lanes(z2), zero_lanes(z3)};
+          uint32_t m16 = 0;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            uint32_t word = e[j], keep = 0;
+            uint32_t word = e[j];
             while (word) {
               const int bit = __ffs(word) - 1;  // 7, 15, 23 or 31
               word &= word - 1;
-              const long long q = (long long)(pos0 + 4 * j + (bit >> 3)) - (long long)pat.anchor;
-              if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) keep |= 1u << bit;
+              const int byte = 4 * j + (bit >> 3);
+              const long long q = (long long)(pos0 + byte) - (long long)pat.anchor;
+              if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) m16 |= 1u << byte;
             }
-            e[j] = keep;
           }
-          f0 = e[0]; f1 = e[1]; f2 = e[2]; f3 = e[3];
-          if (!EMIT) cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+          r.cnt += __popc(m16);
+          if (EMIT) r.mask[u >> 1] |= m16 << (16 * (u & 1));
         }
-      }
-    }
-    if (EMIT) {
-      flags[u][0] = f0; flags[u][1] = f1; flags[u][2] = f2; flags[u][3] = f3;
-      cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
-    }
-  }
-
-  // ---- granule / tile aggregates -----------------------------------------------------------
-  if (NL) {
-    const uint32_t s = warp_sum(nonnl);
-    if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
-  }
-  const uint32_t wcnt = warp_sum(cnt);
-  if (lane == 0) s_warp_cnt[warp] = wcnt;
-  __syncthreads();
-
-  if (!EMIT) {
-    if (threadIdx.x == 0) {
-      uint32_t t = 0;
-#pragma unroll
-      for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
-      a.tile_count[tile] = t;
-    }
-    return;
-  }
-
-  // ---- emit mode: ordered stream compaction ---------------------------------------------------
-  if (warp == 0) {
-    uint32_t t = 0;
-#pragma unroll
-    for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
-    const unsigned long long excl = lookback(a.desc, tile, t, lane);
-    if (lane == 0) {
-      s_tile_base = excl;
-      a.tile_count[tile] = t;
-    }
-  }
-  __syncthreads();
-  if (wcnt == 0) return;  // warp-uniform
-  unsigned long long base = s_tile_base;
-  for (int w = 0; w < warp; ++w) base += s_warp_cnt[w];
-
-#pragma unroll
-  for (int u = 0; u < (EMIT ? kRows : 1); ++u) {
-    const uint32_t c = __popc(flags[u][0]) + __popc(flags[u][1]) + __popc(flags[u][2]) + __popc(flags[u][3]);
-    if (!__any_sync(kFull, c != 0)) continue;
-    uint32_t inc = c;  // inclusive warp scan of the per-lane counts of this row
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(kFull, inc, o);
-      if (lane >= o) inc += t;
-    }
-    unsigned long long slot = base + (inc - c);
-    base += __shfl_sync(kFull, inc, 31);
-    const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes - pat.anchor;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      uint32_t word = flags[u][j];
-      while (word) {
-        const int bit = __ffs(word) - 1;
-        word &= word - 1;
-        if (slot < a.occ_cap) a.occ[slot] = pos0 + 4 * j + (bit >> 3);
-        ++slot;
       }
     }
   }
 }
 
+// ---- count mode: one tile per CTA, per-tile occurrence count (+ newline table) -------------------
+template <int NS, bool NL>
+__global__ void __launch_bounds__(kThreads, 3)
+count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  __shared__ uint32_t s_warp_cnt[kWarps];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const uint64_t tile = blockIdx.x;
+  LaneResult r;
+  scan_granule<NS, false, NL>(pat, a.buf, a.n, tile * (uint64_t)kTileBytes, warp, lane, r);
+  if (NL) {
+    const uint32_t s = warp_sum(r.nonnl);
+    if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
+  }
+  const uint32_t wcnt = warp_sum(r.cnt);
+  if (lane == 0) s_warp_cnt[warp] = wcnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
+    a.tile_count[tile] = t;
+  }
+}
+
+// ---- emit mode: persistent CTAs, ordered stream compaction through decoupled look-back ------------
+template <int NS, bool NL>
+__global__ void __launch_bounds__(kThreads, 4)
+emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  __shared__ uint32_t s_warp_cnt[kWarps];
+  __shared__ unsigned long long s_tile_base;
+  __shared__ unsigned int s_tile;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+
+  if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
+  __syncthreads();
+  uint64_t tile = s_tile;
+  while (tile < a.n_tiles) {
+    // draw the next ticket now; its latency hides behind this tile's work
+    unsigned int next = 0;
+    if (threadIdx.x == 0) next = atomicAdd(a.ticket, 1u);
+
+    const uint64_t tile_off = tile * (uint64_t)kTileBytes;
+    LaneResult r;
+    scan_granule<NS, true, NL>(pat, a.buf, a.n, tile_off, warp, lane, r);
+    if (NL) {
+      const uint32_t s = warp_sum(r.nonnl);
+      if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
+    }
+    const uint32_t wcnt = warp_sum(r.cnt);
+    if (lane == 0) s_warp_cnt[warp] = wcnt;
+    __syncthreads();
+    uint32_t total = 0, before = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const uint32_t c = s_warp_cnt[w];
+      total += c;
+      if (w < warp) before += c;
+    }
+    if (total == 0) {
+      // nothing to place: publish the aggregate so later tiles can look past this one
+      if (threadIdx.x == 0) {
+        st_relaxed_u64(&a.desc[tile], kAggregate);
+        a.tile_count[tile] = 0;
+      }
+    } else {
+      if (warp == 0) {
+        const unsigned long long excl = lookback(a.desc, tile, total, lane);
+        if (lane == 0) {
+          s_tile_base = excl;
+          a.tile_count[tile] = total;
+          atomicAdd(a.occ_total, (unsigned long long)total);
+        }
+      }
+      __syncthreads();
+      if (wcnt != 0) {  // warp-uniform
+        unsigned long long base = s_tile_base + before;
+        const uint64_t lane_off = tile_off + (uint64_t)warp * kGranuleBytes + (uint64_t)lane * 16 - pat.anchor;
+#pragma unroll
+        for (int u = 0; u < kRows; ++u) {
+          uint32_t m16 = (r.mask[u >> 1] >> (16 * (u & 1))) & 0xffffu;
+          const uint32_t c = __popc(m16);
+          if (!__any_sync(kFull, c != 0)) continue;
+          uint32_t inc = c;  // inclusive warp scan of the per-lane counts of this row
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(kFull, inc, o);
+            if (lane >= o) inc += t;
+          }
+          unsigned long long slot = base + (inc - c);
+          base += __shfl_sync(kFull, inc, 31);
+          const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
+          while (m16) {
+            const int b = __ffs(m16) - 1;
+            m16 &= m16 - 1;
+            if (slot < a.occ_cap) a.occ[slot] = pos0 + b;
+            ++slot;
+          }
+        }
+      }
+    }
+    if (threadIdx.x == 0) s_tile = next;
+    __syncthreads();  // also protects s_warp_cnt / s_tile_base for the next iteration
+    tile = s_tile;
+  }
+}
+
 template <int NS>
-void launch_ns(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, cudaStream_t s) {
-  const dim3 grid((unsigned)a.n_tiles), block(kThreads);
+void launch_ns(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s) {
+  const dim3 block(kThreads);
   if (emit) {
-    if (newlines) scan_kernel<NS, true, true><<<grid, block, 0, s>>>(pat, a);
-    else scan_kernel<NS, true, false><<<grid, block, 0, s>>>(pat, a);
+    const uint64_t want = (uint64_t)sm_count * 4;
+    const dim3 grid((unsigned)(a.n_tiles < want ? a.n_tiles : want));
+    if (newlines) emit_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
+    else emit_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
   } else {
-    if (newlines) scan_kernel<NS, false, true><<<grid, block, 0, s>>>(pat, a);
-    else scan_kernel<NS, false, false><<<grid, block, 0, s>>>(pat, a);
+    const dim3 grid((unsigned)a.n_tiles);
+    if (newlines) count_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
+    else count_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
   }
 }
 
 }  // namespace
 
-void launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, cudaStream_t s) {
+void launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s) {
   if (a.n_tiles == 0) return;
   switch (pat.m) {
-    case 1: launch_ns<1>(pat, a, emit, newlines, s); break;
-    case 2: launch_ns<2>(pat, a, emit, newlines, s); break;
-    case 3: launch_ns<3>(pat, a, emit, newlines, s); break;
-    case 4: launch_ns<4>(pat, a, emit, newlines, s); break;
-    default: launch_ns<5>(pat, a, emit, newlines, s); break;
+    case 1: launch_ns<1>(pat, a, emit, newlines, sm_count, s); break;
+    case 2: launch_ns<2>(pat, a, emit, newlines, sm_count, s); break;
+    case 3: launch_ns<3>(pat, a, emit, newlines, sm_count, s); break;
+    case 4: launch_ns<4>(pat, a, emit, newlines, sm_count, s); break;
+    default: launch_ns<5>(pat, a, emit, newlines, sm_count, s); break;
   }
 }
 

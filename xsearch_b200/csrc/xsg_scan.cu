@@ -136,7 +136,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
 
   if (count_only) {
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-    launch_scan(pat, a, false, false, s);
+    launch_scan(pat, a, false, false, ctx->sm_count, s);
     XSG_CUDA(cudaGetLastError());
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
     launch_reduce_u32(a.tile_count, n_tiles, &ds->occ_total, s);
@@ -159,6 +159,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     }
     a.desc = ctx->desc.as<unsigned long long>();
     a.ticket = &ds->ticket[0];
+    a.occ_total = &ds->occ_total;
     uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
     uint64_t k = 0;
     for (int attempt = 0;; ++attempt) {
@@ -167,15 +168,16 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       a.occ_cap = cap;
       XSG_CUDA(cudaMemsetAsync(a.desc, 0, n_tiles * sizeof(unsigned long long), s));
       XSG_CUDA(cudaMemsetAsync(&ds->ticket[0], 0, sizeof(unsigned int), s));
+      XSG_CUDA(cudaMemsetAsync(&ds->occ_total, 0, sizeof(unsigned long long), s));
       XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-      launch_scan(pat, a, true, want_idx, s);
+      launch_scan(pat, a, true, want_idx, ctx->sm_count, s);
       XSG_CUDA(cudaGetLastError());
       XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
       st->launches += 1;
-      unsigned long long last = 0;
-      XSG_CUDA(cudaMemcpyAsync(&last, a.desc + (n_tiles - 1), sizeof last, cudaMemcpyDeviceToHost, s));
+      XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
+                               cudaMemcpyDeviceToHost, s));
       XSG_CUDA(cudaStreamSynchronize(s));
-      k = last & ((1ull << 62) - 1);
+      k = ctx->h_scalars->occ_total;
       if (k <= cap) break;
       if (attempt > 0) {
         set_error("occurrence buffer overflow after retry");
