@@ -16,10 +16,10 @@
 // flight per thread; the pattern-length halo is one extra 32-bit word per row obtained with a warp
 // shuffle (m <= 4 needs <= 3 halo bytes; the m >= 5 filter tests pattern bytes a and a+4).
 //
-// Emit mode is a persistent kernel: CTAs draw tile ids from a ticket counter (the next ticket is
-// fetched while the current tile is processed), keep the per-lane occurrence masks as 16 bits per
-// row (4 registers per thread) across the look-back, and tiles without occurrences publish their
-// aggregate and skip the look-back altogether.
+// Emit mode is a persistent, cooperatively launched kernel: CTA b handles tiles b, b+grid, ... so the
+// predecessors of a tile are in flight in the neighbouring CTAs; the per-lane occurrence masks are kept
+// as 16 bits per row (4 registers per thread) across the look-back, and tiles without occurrences
+// publish their aggregate and skip the look-back altogether.
 #include "xsg_common.cuh"
 
 namespace xsg {
@@ -193,18 +193,12 @@ __global__ void __launch_bounds__(kThreads, 4)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   __shared__ uint32_t s_warp_cnt[kWarps];
   __shared__ unsigned long long s_tile_base;
-  __shared__ unsigned int s_tile;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
 
-  if (threadIdx.x == 0) s_tile = atomicAdd(a.ticket, 1u);
-  __syncthreads();
-  uint64_t tile = s_tile;
-  while (tile < a.n_tiles) {
-    // draw the next ticket now; its latency hides behind this tile's work
-    unsigned int next = 0;
-    if (threadIdx.x == 0) next = atomicAdd(a.ticket, 1u);
-
+  // static strided tile assignment: tile t-1 is processed by the neighbouring CTA in the same round,
+  // so predecessors are always in flight (the grid is launched cooperatively => co-resident)
+  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     const uint64_t tile_off = tile * (uint64_t)kTileBytes;
     LaneResult r;
     scan_granule<NS, true, NL>(pat, a.buf, a.n, tile_off, warp, lane, r);
@@ -264,37 +258,47 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
         }
       }
     }
-    if (threadIdx.x == 0) s_tile = next;
-    __syncthreads();  // also protects s_warp_cnt / s_tile_base for the next iteration
-    tile = s_tile;
+    __syncthreads();  // protects s_warp_cnt / s_tile_base for the next iteration
   }
 }
 
-template <int NS>
-void launch_ns(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s) {
-  const dim3 block(kThreads);
-  if (emit) {
-    const uint64_t want = (uint64_t)sm_count * 4;
-    const dim3 grid((unsigned)(a.n_tiles < want ? a.n_tiles : want));
-    if (newlines) emit_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
-    else emit_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
-  } else {
-    const dim3 grid((unsigned)a.n_tiles);
-    if (newlines) count_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
-    else count_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
+template <int NS, bool NL>
+cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
+  // persistent grid sized to what is co-resident; the cooperative launch makes that a checked
+  // guarantee (it fails instead of dead-locking the look-back if the grid could not be resident)
+  static int per_sm = 0;
+  if (per_sm == 0) {
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emit_kernel<NS, NL>, kThreads, 0);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    if (per_sm > 4) per_sm = 4;
   }
+  const uint64_t want = (uint64_t)sm_count * per_sm;
+  const dim3 grid((unsigned)(a.n_tiles < want ? a.n_tiles : want)), block(kThreads);
+  void* args[] = {const_cast<Pattern*>(&pat), const_cast<ScanArgs*>(&a)};
+  return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(emit_kernel<NS, NL>), grid, block, args, 0, s);
+}
+
+template <int NS>
+cudaError_t launch_ns(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s) {
+  if (emit) return newlines ? launch_emit<NS, true>(pat, a, sm_count, s) : launch_emit<NS, false>(pat, a, sm_count, s);
+  const dim3 grid((unsigned)a.n_tiles), block(kThreads);
+  if (newlines) count_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
+  else count_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
+  return cudaGetLastError();
 }
 
 }  // namespace
 
-void launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s) {
-  if (a.n_tiles == 0) return;
+cudaError_t launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count,
+                        cudaStream_t s) {
+  if (a.n_tiles == 0) return cudaSuccess;
   switch (pat.m) {
-    case 1: launch_ns<1>(pat, a, emit, newlines, sm_count, s); break;
-    case 2: launch_ns<2>(pat, a, emit, newlines, sm_count, s); break;
-    case 3: launch_ns<3>(pat, a, emit, newlines, sm_count, s); break;
-    case 4: launch_ns<4>(pat, a, emit, newlines, sm_count, s); break;
-    default: launch_ns<5>(pat, a, emit, newlines, sm_count, s); break;
+    case 1: return launch_ns<1>(pat, a, emit, newlines, sm_count, s);
+    case 2: return launch_ns<2>(pat, a, emit, newlines, sm_count, s);
+    case 3: return launch_ns<3>(pat, a, emit, newlines, sm_count, s);
+    case 4: return launch_ns<4>(pat, a, emit, newlines, sm_count, s);
+    default: return launch_ns<5>(pat, a, emit, newlines, sm_count, s);
   }
 }
 

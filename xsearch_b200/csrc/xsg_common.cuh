@@ -37,12 +37,12 @@ struct ScanArgs {
   uint64_t* occ;          // raw occurrence list (emit mode) or nullptr
   uint64_t occ_cap;
   unsigned long long* desc;    // [n_tiles] decoupled look-back descriptors (emit mode)
-  unsigned int* ticket;        // dynamic tile id (emit mode)
   unsigned long long* occ_total;  // total number of occurrences (emit mode)
 };
 
 // launchers implemented in scan_kernel.cu
-void launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s);
+cudaError_t launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count,
+                        cudaStream_t s);
 
 // ---- list-domain (post) kernels, list_kernels.cu -------------------------------------------
 struct ListArgs {

@@ -136,8 +136,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
 
   if (count_only) {
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-    launch_scan(pat, a, false, false, ctx->sm_count, s);
-    XSG_CUDA(cudaGetLastError());
+    XSG_CUDA(launch_scan(pat, a, false, false, ctx->sm_count, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
     launch_reduce_u32(a.tile_count, n_tiles, &ds->occ_total, s);
     launch_zone_count(buf, n, d_bounds, nb, pat, a.tile_count, &ds->zone_sub, &ds->zone_add, s);
@@ -158,7 +157,6 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       a.nl_granule = ctx->nl_granule.as<uint32_t>();
     }
     a.desc = ctx->desc.as<unsigned long long>();
-    a.ticket = &ds->ticket[0];
     a.occ_total = &ds->occ_total;
     uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
     uint64_t k = 0;
@@ -167,11 +165,9 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       a.occ = ctx->occ.as<uint64_t>();
       a.occ_cap = cap;
       XSG_CUDA(cudaMemsetAsync(a.desc, 0, n_tiles * sizeof(unsigned long long), s));
-      XSG_CUDA(cudaMemsetAsync(&ds->ticket[0], 0, sizeof(unsigned int), s));
       XSG_CUDA(cudaMemsetAsync(&ds->occ_total, 0, sizeof(unsigned long long), s));
       XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-      launch_scan(pat, a, true, want_idx, ctx->sm_count, s);
-      XSG_CUDA(cudaGetLastError());
+      XSG_CUDA(launch_scan(pat, a, true, want_idx, ctx->sm_count, s));
       XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
       st->launches += 1;
       XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
