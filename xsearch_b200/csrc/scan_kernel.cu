@@ -191,14 +191,16 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
 template <int NS, bool NL>
 __global__ void __launch_bounds__(kThreads, 4)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
-  __shared__ uint32_t s_warp_cnt[kWarps];
+  __shared__ uint32_t s_warp_cnt2[2][kWarps];  // double-buffered: no barrier at the end of a tile
   __shared__ unsigned long long s_tile_base;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
 
   // static strided tile assignment: tile t-1 is processed by the neighbouring CTA in the same round,
   // so predecessors are always in flight (the grid is launched cooperatively => co-resident)
-  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+  int round = 0;
+  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, round ^= 1) {
+    uint32_t* s_warp_cnt = s_warp_cnt2[round];
     const uint64_t tile_off = tile * (uint64_t)kTileBytes;
     LaneResult r;
     scan_granule<NS, true, NL>(pat, a.buf, a.n, tile_off, warp, lane, r);
@@ -258,7 +260,6 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
         }
       }
     }
-    __syncthreads();  // protects s_warp_cnt / s_tile_base for the next iteration
   }
 }
 

@@ -106,8 +106,8 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_s
 
 
 // Decoupled look-back (Merrill & Garland): returns the exclusive prefix of `aggregate` over all
-// tiles before `tile`; called by warp 0 only.  desc[] was zeroed before the launch; tile ids are
-// handed out by a ticket so every predecessor is resident or finished (forward progress).
+// tiles before `tile`; called by warp 0 only.  desc[] was zeroed before the launch; every
+// predecessor tile is owned by a resident CTA (cooperative persistent grid) => forward progress.
 __device__ __forceinline__ unsigned long long lookback(unsigned long long* desc, uint64_t tile,
                                                        unsigned long long aggregate, int lane) {
   if (tile == 0) {
@@ -118,19 +118,19 @@ __device__ __forceinline__ unsigned long long lookback(unsigned long long* desc,
   unsigned long long excl = 0;
   long long idx = (long long)tile - 1;
   while (true) {
-    long long my = idx - lane;
+    const long long my = idx - lane;
     unsigned long long d;
-    unsigned st;
+    unsigned pm, need;
     do {
       d = my >= 0 ? ld_relaxed_u64(&desc[my]) : kPrefix;  // virtual tile -1: prefix 0
-      st = (unsigned)(d >> kStatusShift);
-    } while (__any_sync(kFull, st == 0));
-    unsigned pm = __ballot_sync(kFull, st == 2);
+      const unsigned st = (unsigned)(d >> kStatusShift);
+      pm = __ballot_sync(kFull, st == 2);
+      const unsigned inv = __ballot_sync(kFull, st == 0);
+      // only the tiles between this one and the nearest inclusive prefix have to be published
+      need = pm ? (inv & ((1u << (__ffs(pm) - 1)) - 1u)) : inv;
+    } while (need);
     unsigned long long val = d & kValueMask;
-    if (pm) {
-      int first = __ffs(pm) - 1;  // nearest predecessor holding an inclusive prefix
-      if (lane > first) val = 0;
-    }
+    if (pm && lane > __ffs(pm) - 1) val = 0;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(kFull, val, o);
     excl += val;
