@@ -49,22 +49,16 @@ struct LaneResult {
   uint32_t nonnl;            // bytes that are not '\n' (zero padding included)
 };
 
-// Phase 1 for one warp granule: load, classify, (verify), count.  NS: 1..4 = exact compare of m = NS
-// consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification.
-template <int NS, bool EMIT, bool NL>
-__device__ __forceinline__ void scan_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
-                                             uint64_t tile_off, int warp, int lane, LaneResult& r) {
-  const uint64_t gran_off = tile_off + (uint64_t)warp * kGranuleBytes;
+// Loads one warp granule: 8 independent coalesced 16-byte loads per thread (+ the halo word in lane 0).
+__device__ __forceinline__ void load_granule(const uint8_t* __restrict__ buf, uint64_t n, uint64_t gran_off, int lane,
+                                             uint4 (&v)[kRows], uint32_t& ext) {
   const uint64_t lane_off = gran_off + (uint64_t)lane * 16;
-  const bool partial = tile_off + kTileBytes + 16 > n;
-
-  // ---- load the granule: 8 independent coalesced 16-byte loads per thread -------------------
-  uint4 v[kRows];
-  uint32_t ext = 0;  // lane 0: first word behind the granule (halo of the last row)
+  const bool partial = gran_off + kGranuleBytes + 16 > n;
+  ext = 0;  // lane 0: first word behind the granule (halo of the last row)
   if (!partial) {
 #pragma unroll
     for (int u = 0; u < kRows; ++u) v[u] = ld_stream_v4(reinterpret_cast<const uint4*>(buf + lane_off + u * kRowBytes));
-    if (lane == 0) ext = __ldg(reinterpret_cast<const uint32_t*>(buf + gran_off + kGranuleBytes));
+    if (lane == 0) ext = ld_stream_u32(reinterpret_cast<const uint32_t*>(buf + gran_off + kGranuleBytes));
   } else {
 #pragma unroll
     for (int u = 0; u < kRows; ++u) {
@@ -82,9 +76,19 @@ __device__ __forceinline__ void scan_granule(const Pattern& pat, const uint8_t* 
     }
     if (lane == 0) {
       const uint64_t pos = gran_off + kGranuleBytes;
-      if (pos < n) ext = keep_lanes(__ldg(reinterpret_cast<const uint32_t*>(buf + pos)), (long long)(n - pos));
+      if (pos < n) ext = keep_lanes(ld_stream_u32(reinterpret_cast<const uint32_t*>(buf + pos)), (long long)(n - pos));
     }
   }
+}
+
+// Phase 1 for one warp granule: classify, (verify), count.  NS: 1..4 = exact compare of m = NS
+// consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification.
+template <int NS, bool EMIT, bool NL>
+__device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
+                                                 uint64_t gran_off, int lane, const uint4 (&v)[kRows], uint32_t ext,
+                                                 LaneResult& r) {
+  const uint64_t lane_off = gran_off + (uint64_t)lane * 16;
+  const bool partial = gran_off + kGranuleBytes + 16 > n;
 
   r.cnt = 0;
   r.nonnl = 0;
@@ -170,8 +174,12 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const uint64_t tile = blockIdx.x;
+  const uint64_t gran_off = tile * (uint64_t)kTileBytes + (uint64_t)warp * kGranuleBytes;
+  uint4 v[kRows];
+  uint32_t ext;
+  load_granule(a.buf, a.n, gran_off, lane, v, ext);
   LaneResult r;
-  scan_granule<NS, false, NL>(pat, a.buf, a.n, tile * (uint64_t)kTileBytes, warp, lane, r);
+  classify_granule<NS, false, NL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
   if (NL) {
     const uint32_t s = warp_sum(r.nonnl);
     if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
@@ -189,7 +197,7 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
 
 // ---- emit mode: persistent CTAs, ordered stream compaction through decoupled look-back ------------
 template <int NS, bool NL>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   __shared__ uint32_t s_warp_cnt2[2][kWarps];  // double-buffered: no barrier at the end of a tile
   __shared__ unsigned long long s_tile_base;
@@ -198,12 +206,20 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
 
   // static strided tile assignment: tile t-1 is processed by the neighbouring CTA in the same round,
   // so predecessors are always in flight (the grid is launched cooperatively => co-resident)
+  // Software pipeline: the loads of the next tile are issued before this tile's barrier / look-back /
+  // emission, so HBM stays busy while the CTA waits on its predecessors.
   int round = 0;
+  uint4 v[kRows];
+  uint32_t ext = 0;
+  if (blockIdx.x < a.n_tiles)
+    load_granule(a.buf, a.n, blockIdx.x * (uint64_t)kTileBytes + (uint64_t)warp * kGranuleBytes, lane, v, ext);
   for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, round ^= 1) {
     uint32_t* s_warp_cnt = s_warp_cnt2[round];
     const uint64_t tile_off = tile * (uint64_t)kTileBytes;
     LaneResult r;
-    scan_granule<NS, true, NL>(pat, a.buf, a.n, tile_off, warp, lane, r);
+    classify_granule<NS, true, NL>(pat, a.buf, a.n, tile_off + (uint64_t)warp * kGranuleBytes, lane, v, ext, r);
+    if (tile + gridDim.x < a.n_tiles)
+      load_granule(a.buf, a.n, (tile + gridDim.x) * (uint64_t)kTileBytes + (uint64_t)warp * kGranuleBytes, lane, v, ext);
     if (NL) {
       const uint32_t s = warp_sum(r.nonnl);
       if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;

@@ -78,6 +78,12 @@ __device__ __forceinline__ uint4 ld_stream_v4(const uint4* p) {
   return r;
 }
 
+__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
+  uint32_t r;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+
 constexpr uint32_t k7F = 0x7f7f7f7fu;
 constexpr uint32_t k80 = 0x80808080u;
 constexpr uint32_t k01 = 0x01010101u;
