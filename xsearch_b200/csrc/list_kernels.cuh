@@ -33,7 +33,7 @@ void launch_zone(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s
 // count-only variant without an occurrence list: adds to sub (true occurrences inside the tail zones)
 // and add (occurrences the reference reports there)
 void launch_zone_count(const uint8_t* buf, uint64_t n, const uint64_t* bounds, uint64_t nb, const Pattern& pat,
-                       const uint32_t* tile_count, unsigned long long* sub, unsigned long long* add, cudaStream_t s);
+                       const uint32_t* gran_count, unsigned long long* sub, unsigned long long* add, cudaStream_t s);
 
 struct CompactArgs {
   ListArgs l;

@@ -1,13 +1,17 @@
-// scan_kernel.cu -- the byte-scanning kernel (sm_100a): one pass over the corpus that
+// scan_kernel.cu -- the byte-scanning kernels (sm_100a).
+//
+// Pass 1 (count_kernel) reads every byte once and
 //   * finds every true occurrence of the literal (exact SIMD-in-word compare for m <= 4, a two-byte
-//     SIMD filter + verification for m >= 5),
-//   * counts '\n' per 4 KiB granule (line-index accounting), and
-//   * either counts occurrences per tile or emits them, in file order, through a single-pass
-//     decoupled look-back scan (stream compaction).
+//     SIMD filter + verification for m >= 5), storing one counter per 4 KiB granule, and
+//   * counts '\n' per 4 KiB granule (line-index accounting).
+// Pass 2 (emit_kernel) re-reads only the granules that hold occurrences and writes their positions,
+// in file order, at the exclusive prefix of the granule counters (stream compaction without any
+// inter-CTA dependency; a decoupled look-back variant stalled on descriptor latency under full HBM
+// load).
 //
 // Replaces the inner loops of the reference: simd::strstr / strchr (simd_search.cpp:116-204) driven
 // by the findNext / findNextNewLine chains of search_wrappers.h:36-50,168-183,192-205.  The
-// sequential "next match -> skip -> next" chain is reformulated data-parallel: this kernel reports
+// sequential "next match -> skip -> next" chain is reformulated data-parallel: these kernels report
 // ALL true occurrences; greedy non-overlap, first-hit-per-line and the reference's chunk-tail quirk
 // are resolved on the (much smaller) occurrence list by list_kernels.cu.
 //
@@ -15,11 +19,6 @@
 // => every load is one fully coalesced 16-byte ld.global.nc per thread, 8 independent loads in
 // flight per thread; the pattern-length halo is one extra 32-bit word per row obtained with a warp
 // shuffle (m <= 4 needs <= 3 halo bytes; the m >= 5 filter tests pattern bytes a and a+4).
-//
-// Emit mode is a persistent, cooperatively launched kernel: CTA b handles tiles b, b+grid, ... so the
-// predecessors of a tile are in flight in the neighbouring CTAs; the per-lane occurrence masks are kept
-// as 16 bits per row (4 registers per thread) across the look-back, and tiles without occurrences
-// publish their aggregate and skip the look-back altogether.
 #include "xsg_common.cuh"
 
 namespace xsg {
@@ -166,15 +165,15 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
   }
 }
 
-// ---- count mode: one tile per CTA, per-tile occurrence count (+ newline table) -------------------
+// ---- pass 1: every byte once; per-granule occurrence counts (+ newline table) -----------------------
+// No inter-warp communication at all: each warp owns its granule and writes its own counters.
 template <int NS, bool NL>
 __global__ void __launch_bounds__(kThreads, 3)
 count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
-  __shared__ uint32_t s_warp_cnt[kWarps];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const uint64_t tile = blockIdx.x;
-  const uint64_t gran_off = tile * (uint64_t)kTileBytes + (uint64_t)warp * kGranuleBytes;
+  const uint64_t g = (uint64_t)blockIdx.x * kWarps + warp;
+  const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
   uint4 v[kRows];
   uint32_t ext;
   load_granule(a.buf, a.n, gran_off, lane, v, ext);
@@ -182,140 +181,102 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   classify_granule<NS, false, NL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
   if (NL) {
     const uint32_t s = warp_sum(r.nonnl);
-    if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
+    if (lane == 0) a.nl_granule[g] = kGranuleBytes - s;
   }
   const uint32_t wcnt = warp_sum(r.cnt);
-  if (lane == 0) s_warp_cnt[warp] = wcnt;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t t = 0;
-#pragma unroll
-    for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
-    a.tile_count[tile] = t;
-  }
+  if (lane == 0) a.gran_count[g] = wcnt;
 }
 
-// ---- emit mode: persistent CTAs, ordered stream compaction through decoupled look-back ------------
-template <int NS, bool NL>
+// ---- pass 2: ordered emission.  Only granules that hold occurrences are read again; their output
+// position is the exclusive prefix of the granule counts, so there is no inter-CTA dependency.
+// A warp inspects 32 granule counters at a time and re-classifies the non-empty ones.
+template <int NS>
 __global__ void __launch_bounds__(kThreads, 3)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
-  __shared__ uint32_t s_warp_cnt2[2][kWarps];  // double-buffered: no barrier at the end of a tile
-  __shared__ unsigned long long s_tile_base;
   const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-
-  // static strided tile assignment: tile t-1 is processed by the neighbouring CTA in the same round,
-  // so predecessors are always in flight (the grid is launched cooperatively => co-resident)
-  // Software pipeline: the loads of the next tile are issued before this tile's barrier / look-back /
-  // emission, so HBM stays busy while the CTA waits on its predecessors.
-  int round = 0;
-  uint4 v[kRows];
-  uint32_t ext = 0;
-  if (blockIdx.x < a.n_tiles)
-    load_granule(a.buf, a.n, blockIdx.x * (uint64_t)kTileBytes + (uint64_t)warp * kGranuleBytes, lane, v, ext);
-  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, round ^= 1) {
-    uint32_t* s_warp_cnt = s_warp_cnt2[round];
-    const uint64_t tile_off = tile * (uint64_t)kTileBytes;
-    LaneResult r;
-    classify_granule<NS, true, NL>(pat, a.buf, a.n, tile_off + (uint64_t)warp * kGranuleBytes, lane, v, ext, r);
-    if (tile + gridDim.x < a.n_tiles)
-      load_granule(a.buf, a.n, (tile + gridDim.x) * (uint64_t)kTileBytes + (uint64_t)warp * kGranuleBytes, lane, v, ext);
-    if (NL) {
-      const uint32_t s = warp_sum(r.nonnl);
-      if (lane == 0) a.nl_granule[tile * kWarps + warp] = kGranuleBytes - s;
-    }
-    const uint32_t wcnt = warp_sum(r.cnt);
-    if (lane == 0) s_warp_cnt[warp] = wcnt;
-    __syncthreads();
-    uint32_t total = 0, before = 0;
+  const uint64_t warp_global = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+  const uint64_t total_warps = (uint64_t)gridDim.x * kWarps;
+  const uint64_t n_gran = a.n_tiles * kWarps;
+  for (uint64_t g0 = warp_global * 32; g0 < n_gran; g0 += total_warps * 32) {
+    const uint64_t gi = g0 + lane;
+    const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
+    unsigned todo = __ballot_sync(kFull, c != 0);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint64_t g = g0 + src;
+      const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
+      uint4 v[kRows];
+      uint32_t ext;
+      load_granule(a.buf, a.n, gran_off, lane, v, ext);
+      unsigned long long base = a.gran_prefix[g];
+      LaneResult r;
+      classify_granule<NS, true, false>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
+      const uint64_t lane_off = gran_off + (uint64_t)lane * 16 - pat.anchor;
 #pragma unroll
-    for (int w = 0; w < kWarps; ++w) {
-      const uint32_t c = s_warp_cnt[w];
-      total += c;
-      if (w < warp) before += c;
-    }
-    if (total == 0) {
-      // nothing to place: publish the aggregate so later tiles can look past this one
-      if (threadIdx.x == 0) {
-        st_relaxed_u64(&a.desc[tile], kAggregate);
-        a.tile_count[tile] = 0;
-      }
-    } else {
-      if (warp == 0) {
-        const unsigned long long excl = lookback(a.desc, tile, total, lane);
-        if (lane == 0) {
-          s_tile_base = excl;
-          a.tile_count[tile] = total;
-          atomicAdd(a.occ_total, (unsigned long long)total);
+      for (int u = 0; u < kRows; ++u) {
+        uint32_t m16 = (r.mask[u >> 1] >> (16 * (u & 1))) & 0xffffu;
+        const uint32_t cu = __popc(m16);
+        if (!__any_sync(kFull, cu != 0)) continue;
+        uint32_t inc = cu;  // inclusive warp scan of the per-lane counts of this row
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(kFull, inc, o);
+          if (lane >= o) inc += t;
         }
-      }
-      __syncthreads();
-      if (wcnt != 0) {  // warp-uniform
-        unsigned long long base = s_tile_base + before;
-        const uint64_t lane_off = tile_off + (uint64_t)warp * kGranuleBytes + (uint64_t)lane * 16 - pat.anchor;
-#pragma unroll
-        for (int u = 0; u < kRows; ++u) {
-          uint32_t m16 = (r.mask[u >> 1] >> (16 * (u & 1))) & 0xffffu;
-          const uint32_t c = __popc(m16);
-          if (!__any_sync(kFull, c != 0)) continue;
-          uint32_t inc = c;  // inclusive warp scan of the per-lane counts of this row
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(kFull, inc, o);
-            if (lane >= o) inc += t;
-          }
-          unsigned long long slot = base + (inc - c);
-          base += __shfl_sync(kFull, inc, 31);
-          const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
-          while (m16) {
-            const int b = __ffs(m16) - 1;
-            m16 &= m16 - 1;
-            if (slot < a.occ_cap) a.occ[slot] = pos0 + b;
-            ++slot;
-          }
+        unsigned long long slot = base + (inc - cu);
+        base += __shfl_sync(kFull, inc, 31);
+        const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
+        while (m16) {
+          const int b = __ffs(m16) - 1;
+          m16 &= m16 - 1;
+          if (slot < a.occ_cap) a.occ[slot] = pos0 + b;
+          ++slot;
         }
       }
     }
   }
-}
-
-template <int NS, bool NL>
-cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
-  // persistent grid sized to what is co-resident; the cooperative launch makes that a checked
-  // guarantee (it fails instead of dead-locking the look-back if the grid could not be resident)
-  static int per_sm = 0;
-  if (per_sm == 0) {
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emit_kernel<NS, NL>, kThreads, 0);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    if (per_sm > 4) per_sm = 4;
-  }
-  const uint64_t want = (uint64_t)sm_count * per_sm;
-  const dim3 grid((unsigned)(a.n_tiles < want ? a.n_tiles : want)), block(kThreads);
-  void* args[] = {const_cast<Pattern*>(&pat), const_cast<ScanArgs*>(&a)};
-  return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(emit_kernel<NS, NL>), grid, block, args, 0, s);
 }
 
 template <int NS>
-cudaError_t launch_ns(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count, cudaStream_t s) {
-  if (emit) return newlines ? launch_emit<NS, true>(pat, a, sm_count, s) : launch_emit<NS, false>(pat, a, sm_count, s);
+cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
   if (newlines) count_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
   else count_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
   return cudaGetLastError();
 }
 
+template <int NS>
+cudaError_t launch_emit_ns(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
+  const uint64_t blocks32 = div_up(a.n_tiles * kWarps, 32);          // units of 32 granules
+  const uint64_t want = (uint64_t)sm_count * 6;                        // persistent: a few CTAs per SM
+  const uint64_t need = div_up(blocks32, kWarps);
+  const dim3 grid((unsigned)(need < want ? need : want)), block(kThreads);
+  emit_kernel<NS><<<grid, block, 0, s>>>(pat, a);
+  return cudaGetLastError();
+}
+
 }  // namespace
 
-cudaError_t launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count,
-                        cudaStream_t s) {
+cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
   switch (pat.m) {
-    case 1: return launch_ns<1>(pat, a, emit, newlines, sm_count, s);
-    case 2: return launch_ns<2>(pat, a, emit, newlines, sm_count, s);
-    case 3: return launch_ns<3>(pat, a, emit, newlines, sm_count, s);
-    case 4: return launch_ns<4>(pat, a, emit, newlines, sm_count, s);
-    default: return launch_ns<5>(pat, a, emit, newlines, sm_count, s);
+    case 1: return launch_count_ns<1>(pat, a, newlines, s);
+    case 2: return launch_count_ns<2>(pat, a, newlines, s);
+    case 3: return launch_count_ns<3>(pat, a, newlines, s);
+    case 4: return launch_count_ns<4>(pat, a, newlines, s);
+    default: return launch_count_ns<5>(pat, a, newlines, s);
+  }
+}
+
+cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
+  if (a.n_tiles == 0) return cudaSuccess;
+  switch (pat.m) {
+    case 1: return launch_emit_ns<1>(pat, a, sm_count, s);
+    case 2: return launch_emit_ns<2>(pat, a, sm_count, s);
+    case 3: return launch_emit_ns<3>(pat, a, sm_count, s);
+    case 4: return launch_emit_ns<4>(pat, a, sm_count, s);
+    default: return launch_emit_ns<5>(pat, a, sm_count, s);
   }
 }
 

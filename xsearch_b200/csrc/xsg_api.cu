@@ -99,7 +99,7 @@ void xsg_destroy(xsg_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   cudaStreamSynchronize(c->copy_stream);
-  Scratch* all[] = {&c->tile_count, &c->nl_granule, &c->nl_prefix, &c->scan_tmp, &c->desc, &c->occ,
+  Scratch* all[] = {&c->gran_count, &c->gran_prefix, &c->nl_granule, &c->nl_prefix, &c->scan_tmp, &c->occ,
                     &c->sel, &c->desc2, &c->stage[0], &c->stage[1], &c->seg_bounds};
   for (Scratch* s : all) s->release();
   for (auto& ev : c->ev) cudaEventDestroy(ev);

@@ -29,20 +29,19 @@ struct Pattern {
 
 // ---- scan kernel launch arguments ---------------------------------------------------------
 struct ScanArgs {
-  const uint8_t* buf;     // corpus bytes, 16-byte aligned
-  uint64_t n;             // corpus size in bytes
-  uint64_t n_tiles;
-  uint32_t* tile_count;   // [n_tiles] occurrences owned by each tile (ownership by anchor byte)
-  uint32_t* nl_granule;   // [n_tiles * kWarps] '\n' per 4 KiB granule (newline mode) or nullptr
-  uint64_t* occ;          // raw occurrence list (emit mode) or nullptr
+  const uint8_t* buf;        // corpus bytes, 16-byte aligned
+  uint64_t n;                // corpus size in bytes
+  uint64_t n_tiles;          // CTAs of pass 1; n_tiles * kWarps granules
+  uint32_t* gran_count;      // [granules] occurrences owned by each 4 KiB granule (ownership by anchor byte)
+  uint32_t* nl_granule;      // [granules] '\n' per granule (newline mode) or nullptr
+  const uint64_t* gran_prefix;  // [granules] exclusive prefix of gran_count (pass 2)
+  uint64_t* occ;             // raw occurrence list (pass 2)
   uint64_t occ_cap;
-  unsigned long long* desc;    // [n_tiles] decoupled look-back descriptors (emit mode)
-  unsigned long long* occ_total;  // total number of occurrences (emit mode)
 };
 
 // launchers implemented in scan_kernel.cu
-cudaError_t launch_scan(const Pattern& pat, const ScanArgs& a, bool emit, bool newlines, int sm_count,
-                        cudaStream_t s);
+cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, cudaStream_t s);
+cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s);
 
 // ---- list-domain (post) kernels, list_kernels.cu -------------------------------------------
 struct ListArgs {

@@ -49,7 +49,7 @@ struct xsg_ctx {
   cudaStream_t stream = nullptr;       // compute
   cudaStream_t copy_stream = nullptr;  // H2D of streamed segments
   cudaEvent_t ev[6] = {};
-  xsg::Scratch tile_count, nl_granule, nl_prefix, scan_tmp, desc, occ, sel, desc2;
+  xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2;
   xsg::Scratch stage[2];               // streamed segments (double buffer)
   xsg::Scratch seg_bounds;
   cudaEvent_t stage_copied[2] = {}, stage_free[2] = {};

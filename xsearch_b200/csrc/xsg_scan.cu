@@ -2,7 +2,8 @@
 //
 // Stages (the reference's chunk -> search -> result loop, Searcher.h:100-120, as stream-ordered
 // kernel launches):
-//   A  scan_kernel      : every byte once; all true occurrences (+ '\n' per 4 KiB granule)
+//   A  count / emit     : every byte once -> granule counters (+ '\n' per 4 KiB granule); positions of
+//                         the occurrences from the granules that hold any
 //   B  select / zone    : reference semantics on the occurrence list (greedy, per-line, chunk tail)
 //   C  compact          : stable compaction + formatting of the requested result vectors
 #include <algorithm>
@@ -125,21 +126,22 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   // xs::count alone with a pattern that cannot overlap itself needs no occurrence list
   const bool count_only = kinds == XSG_COUNT && !pat.bordered;
   const uint64_t n_tiles = div_up(n, kTileBytes);
+  const uint64_t n_gran = n_tiles * kWarps;
   int rc;
-  if ((rc = ctx->tile_count.reserve(n_tiles * sizeof(uint32_t)))) return rc;
+  if ((rc = ctx->gran_count.reserve(n_gran * sizeof(uint32_t)))) return rc;
   ScanArgs a{};
   a.buf = buf;
   a.n = n;
   a.n_tiles = n_tiles;
-  a.tile_count = ctx->tile_count.as<uint32_t>();
+  a.gran_count = ctx->gran_count.as<uint32_t>();
   DevScalars* ds = ctx->d_scalars;
 
   if (count_only) {
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-    XSG_CUDA(launch_scan(pat, a, false, false, ctx->sm_count, s));
+    XSG_CUDA(launch_count(pat, a, false, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
-    launch_reduce_u32(a.tile_count, n_tiles, &ds->occ_total, s);
-    launch_zone_count(buf, n, d_bounds, nb, pat, a.tile_count, &ds->zone_sub, &ds->zone_add, s);
+    launch_reduce_u32(a.gran_count, n_gran, &ds->occ_total, s);
+    launch_zone_count(buf, n, d_bounds, nb, pat, a.gran_count, &ds->zone_sub, &ds->zone_add, s);
     XSG_CUDA(cudaGetLastError());
     st->launches += 2 + (pat.m > 1 ? 1 : 0);
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
@@ -148,27 +150,31 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     st->raw += h.occ_total;
     part->n_match = h.occ_total - h.zone_sub + h.zone_add;
   } else {
-    if ((rc = ctx->desc.reserve(n_tiles * sizeof(unsigned long long)))) return rc;
+    if ((rc = ctx->gran_prefix.reserve((n_gran + 1) * sizeof(uint64_t)))) return rc;
+    if ((rc = ctx->scan_tmp.reserve((div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
     if (want_idx) {
-      const uint64_t n_gran = n_tiles * kWarps;
       if ((rc = ctx->nl_granule.reserve(n_gran * sizeof(uint32_t)))) return rc;
       if ((rc = ctx->nl_prefix.reserve((n_gran + 1) * sizeof(uint64_t)))) return rc;
-      if ((rc = ctx->scan_tmp.reserve((div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
       a.nl_granule = ctx->nl_granule.as<uint32_t>();
     }
-    a.desc = ctx->desc.as<unsigned long long>();
-    a.occ_total = &ds->occ_total;
+    a.gran_prefix = ctx->gran_prefix.as<uint64_t>();
+    // pass 1: every byte once -> granule counters; then their exclusive prefix
+    XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
+    XSG_CUDA(launch_count(pat, a, want_idx, s));
+    XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
+    launch_exscan_u32(a.gran_count, n_gran, ctx->gran_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
+                      &ds->occ_total, s);
+    XSG_CUDA(cudaGetLastError());
+    st->launches += 4;
+    // pass 2: positions of the occurrences (re-reads only granules that hold any)
     uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
+    if (ctx->occ.cap / sizeof(uint64_t) > cap && !occ_cap_opt) cap = ctx->occ.cap / sizeof(uint64_t);
     uint64_t k = 0;
     for (int attempt = 0;; ++attempt) {
       if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
       a.occ = ctx->occ.as<uint64_t>();
       a.occ_cap = cap;
-      XSG_CUDA(cudaMemsetAsync(a.desc, 0, n_tiles * sizeof(unsigned long long), s));
-      XSG_CUDA(cudaMemsetAsync(&ds->occ_total, 0, sizeof(unsigned long long), s));
-      XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-      XSG_CUDA(launch_scan(pat, a, true, want_idx, ctx->sm_count, s));
-      XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
+      XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
       st->launches += 1;
       XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
                                cudaMemcpyDeviceToHost, s));
@@ -179,11 +185,11 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         set_error("occurrence buffer overflow after retry");
         return XSG_ERR_STATE;
       }
-      cap = k;  // rare: denser than the estimate -> rescan with the exact capacity
+      cap = k;  // rare: denser than the estimate -> emit again with the exact capacity
     }
     st->raw += k;
     if (want_idx) {
-      launch_exscan_u32(a.nl_granule, n_tiles * kWarps, ctx->nl_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
+      launch_exscan_u32(a.nl_granule, n_gran, ctx->nl_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
                         &ds->nl_total, s);
       st->launches += 3;
     }
