@@ -95,6 +95,10 @@ int xsg_version(void);
 int xsg_init(int device, xsg_ctx** out);
 void xsg_destroy(xsg_ctx* ctx);
 int xsg_device_info(xsg_ctx* ctx, int* sm_count, uint64_t* total_mem, char* name, size_t name_cap);
+/* run all device work of this context on a caller-owned CUDA stream (a cudaStream_t passed as
+ * void*; NULL = back to the context's own stream).  Lets the caller bracket scans with its own
+ * events and order them with its own work (e.g. an NCCL exchange of shard counts). */
+int xsg_set_stream(xsg_ctx* ctx, void* cuda_stream);
 
 /* pinned host memory for xsg_search_host / xsg_corpus_upload sources (cudaHostAlloc) */
 int xsg_host_alloc(uint64_t n, void** out);
@@ -141,6 +145,10 @@ const uint64_t* xsg_result_device_ptr(const xsg_result* r, uint32_t kind);
 uint64_t xsg_result_newlines(const xsg_result* r);        /* '\n' in the scanned bytes (line kinds) */
 uint64_t xsg_result_raw_occurrences(const xsg_result* r); /* all true occurrences seen            */
 int xsg_result_timings(const xsg_result* r, xsg_timings* t);
+/* multi-GPU fix-up: add offset_delta to every byte offset and line_index_delta to
+ * every line index of a finished result, on the device -- the global line-number base of a shard
+ * is only known after the exchange of all shards' newline counts. */
+int xsg_result_rebase(xsg_result* r, uint64_t offset_delta, uint64_t line_index_delta);
 void xsg_result_free(xsg_result* r);
 
 #ifdef __cplusplus

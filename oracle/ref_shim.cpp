@@ -45,7 +45,10 @@ uint64_t count_newlines(const xs::strtype& d, uint64_t from, uint64_t to) {
 }
 
 void search_chunk(const char* p, uint64_t n, const std::string& pat, int kind, int skip_to_nl, Part* out) {
-  xs::strtype data(p, p + n);  // the reference searches its own copy of the chunk
+  // the reference searches its own copy of the chunk (reader stage, tasks/readers.h:39-48); the
+  // buffer is reused per thread so that the timed baseline does not pay page faults per chunk
+  thread_local xs::strtype data;
+  data.assign(p, p + n);
   switch (kind) {
     case K_COUNT:
       out->count = xs::search::count(data, pat, skip_to_nl != 0);

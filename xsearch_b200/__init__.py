@@ -41,13 +41,13 @@ TAGS = {
 }
 
 EXPORTS = [
-    "xsg_last_error", "xsg_version", "xsg_init", "xsg_destroy", "xsg_device_info", "xsg_host_alloc",
+    "xsg_last_error", "xsg_version", "xsg_init", "xsg_destroy", "xsg_device_info", "xsg_set_stream", "xsg_host_alloc",
     "xsg_host_free", "xsg_corpus_alloc", "xsg_corpus_wrap", "xsg_corpus_free", "xsg_corpus_size",
     "xsg_corpus_device_ptr", "xsg_corpus_upload", "xsg_corpus_download", "xsg_corpus_fill_synth",
     "xsg_corpus_chunk", "xsg_corpus_set_bounds", "xsg_corpus_num_chunks", "xsg_corpus_get_bounds",
     "xsg_synth_host", "xsg_chunk_bounds_host", "xsg_scan", "xsg_search_host", "xsg_result_count",
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
-    "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_free",
+    "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_result_free",
 ]
 
 
@@ -94,6 +94,7 @@ def _load() -> C.CDLL:
         "xsg_init": (i32, [i32, C.POINTER(vp)]),
         "xsg_destroy": (None, [vp]),
         "xsg_device_info": (i32, [vp, C.POINTER(i32), pu64, C.c_char_p, C.c_size_t]),
+        "xsg_set_stream": (i32, [vp, vp]),
         "xsg_host_alloc": (i32, [u64, C.POINTER(vp)]),
         "xsg_host_free": (None, [vp]),
         "xsg_corpus_alloc": (i32, [vp, u64, C.POINTER(vp)]),
@@ -120,6 +121,7 @@ def _load() -> C.CDLL:
         "xsg_result_newlines": (u64, [vp]),
         "xsg_result_raw_occurrences": (u64, [vp]),
         "xsg_result_timings": (i32, [vp, C.POINTER(Timings)]),
+        "xsg_result_rebase": (i32, [vp, u64, u64]),
         "xsg_result_free": (None, [vp]),
     }
     for name, (res, args) in sig.items():

@@ -71,6 +71,10 @@ class Context:
         _check(lib.xsg_device_info(self._h, C.byref(sm), C.byref(mem), name, 128))
         return {"sm_count": sm.value, "total_mem": mem.value, "name": name.value.decode()}
 
+    def set_stream(self, cuda_stream: int) -> None:
+        """Run the context's device work on a caller-owned CUDA stream (0/None = its own stream)."""
+        _check(lib.xsg_set_stream(self._h, C.c_void_p(cuda_stream or None)))
+
     # -- corpora ----------------------------------------------------------------------------
     def corpus(self, n_bytes: int) -> "Corpus":
         h = C.c_void_p()
@@ -209,6 +213,10 @@ class Result:
     @property
     def raw_occurrences(self) -> int:
         return int(lib.xsg_result_raw_occurrences(self._h))
+
+    def rebase(self, offset_delta: int = 0, line_index_delta: int = 0) -> None:
+        """Multi-GPU fix-up: add the shard's global byte / line-number base on the device."""
+        _check(lib.xsg_result_rebase(self._h, offset_delta, line_index_delta))
 
     def timings(self) -> Timings:
         t = Timings()

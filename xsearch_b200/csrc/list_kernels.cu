@@ -190,7 +190,18 @@ __global__ void __launch_bounds__(kScanThreads) exscan_apply_kernel(const uint32
   }
 }
 
+__global__ void add_u64_kernel(uint64_t* v, uint64_t n, uint64_t delta) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    v[i] += delta;
+}
+
 }  // namespace
+
+void launch_add_u64(uint64_t* v, uint64_t n, uint64_t delta, cudaStream_t s) {
+  if (n == 0 || delta == 0) return;
+  const uint64_t want = div_up(n, 256);
+  add_u64_kernel<<<(unsigned)(want < 4736 ? want : 4736), 256, 0, s>>>(v, n, delta);
+}
 
 void launch_synth(uint8_t* dst, uint64_t first_block, uint64_t n_blocks, const xsg_synth_params& p, cudaStream_t s) {
   if (n_blocks == 0) return;

@@ -45,11 +45,15 @@ struct CompactArgs {
   uint64_t* out_line_idx;
   uint64_t* out_line_start;    // xs::lines: (start, len)
   uint64_t* out_line_len;
+  uint64_t* selq;              // [k] scratch: compacted positions of the selected occurrences (line kinds)
   unsigned long long* desc;    // [div_up(k, 2048)] zeroed look-back descriptors
   unsigned int* ticket;        // zeroed
   unsigned long long* total;   // number of selected entries
   unsigned int* unterminated;  // set when the last selected line has no '\n' (xs::lines drops it)
 };
 void launch_compact(const CompactArgs& a, const Pattern& pat, cudaStream_t s);
+
+// v[i] += delta (multi-GPU rebase of offsets / line indices)
+void launch_add_u64(uint64_t* v, uint64_t n, uint64_t delta, cudaStream_t s);
 
 }  // namespace xsg

@@ -39,13 +39,19 @@ __device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t
   return true;
 }
 
-// flags at bits 7/15/23/31 of f -> 4 bits in lane order
-__device__ __forceinline__ uint32_t nibble_of(uint32_t f) { return (f * 0x00204081u) >> 28; }
+// acc + 128 * (number of bytes of w that differ from '\n').  Exact per-lane test in three logic/add
+// operations: bit 7 of ((w ^ c) & 0x7f) + 0x7f is set iff the low seven bits differ from c; bit 7 of
+// w itself differs from c iff it is set (c = 0x0a has it clear), so the xor is not needed for the
+// final OR.  The four 0x80 flags are summed by one dp4a instead of popc + add.
+__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc) {
+  const uint32_t b = ((w ^ 0x0a0a0a0au) & k7F) + k7F;
+  return __dp4a((b | w) & k80, k01, acc);
+}
 
 struct LaneResult {
   uint32_t mask[kRows / 2];  // EMIT: 16 occurrence bits per row, two rows per register
   uint32_t cnt;              // occurrences owned by this lane
-  uint32_t nonnl;            // bytes that are not '\n' (zero padding included)
+  uint32_t nonnl;            // 128 x bytes that are not '\n' (zero padding included)
 };
 
 // Loads one warp granule: 8 independent coalesced 16-byte loads per thread (+ the halo word in lane 0).
@@ -104,9 +110,11 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
     const uint32_t w4 = __shfl_sync(kFull, send, (lane + 1) & 31);
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
-    if (NL) {
-      r.nonnl += __popc(nonzero_lanes(w0 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w1 ^ 0x0a0a0a0au)) +
-                 __popc(nonzero_lanes(w2 ^ 0x0a0a0a0au)) + __popc(nonzero_lanes(w3 ^ 0x0a0a0a0au));
+    if (NL) {  // 128 x (bytes that are not '\n'), accumulated on the multiply-add pipe
+      r.nonnl = not_newline_x128(w0, r.nonnl);
+      r.nonnl = not_newline_x128(w1, r.nonnl);
+      r.nonnl = not_newline_x128(w2, r.nonnl);
+      r.nonnl = not_newline_x128(w3, r.nonnl);
     }
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
@@ -132,7 +140,7 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
       }
       r.cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
       if (EMIT && (f0 | f1 | f2 | f3)) {
-        const uint32_t m16 = nibble_of(f0) | (nibble_of(f1) << 4) | (nibble_of(f2) << 8) | (nibble_of(f3) << 12);
+        const uint32_t m16 = nibble16(f0) | (nibble16(f1) << 4) | (nibble16(f2) << 8) | (nibble16(f3) << 12);
         r.mask[u >> 1] |= m16 << (16 * (u & 1));
       }
     } else {
@@ -165,9 +173,11 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
   }
 }
 
-// ---- pass 1: every byte once; per-granule occurrence counts (+ newline table) -----------------------
-// No inter-warp communication at all: each warp owns its granule and writes its own counters.
-template <int NS, bool NL>
+// ---- pass 1: every byte once; per-granule occurrence counts (+ newline table, + occurrence masks) ----
+// No inter-warp communication at all: each warp owns its granule and writes its own counters.  With
+// MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
+// an occurrence, so pass 2 never touches the corpus again.
+template <int NS, bool NL, bool MASK>
 __global__ void __launch_bounds__(kThreads, 3)
 count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
@@ -178,20 +188,20 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   uint32_t ext;
   load_granule(a.buf, a.n, gran_off, lane, v, ext);
   LaneResult r;
-  classify_granule<NS, false, NL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
+  classify_granule<NS, MASK, NL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
   if (NL) {
-    const uint32_t s = warp_sum(r.nonnl);
+    const uint32_t s = warp_sum(r.nonnl) >> 7;
     if (lane == 0) a.nl_granule[g] = kGranuleBytes - s;
   }
   const uint32_t wcnt = warp_sum(r.cnt);
   if (lane == 0) a.gran_count[g] = wcnt;
+  if (MASK && wcnt != 0) a.gran_mask[g * 32 + lane] = make_uint4(r.mask[0], r.mask[1], r.mask[2], r.mask[3]);
 }
 
-// ---- pass 2: ordered emission.  Only granules that hold occurrences are read again; their output
-// position is the exclusive prefix of the granule counts, so there is no inter-CTA dependency.
-// A warp inspects 32 granule counters at a time and re-classifies the non-empty ones.
-template <int NS>
-__global__ void __launch_bounds__(kThreads, 3)
+// ---- pass 2: ordered emission from the stored masks.  The output position of a granule is the
+// exclusive prefix of the granule counts, so there is no inter-CTA dependency.  A warp inspects 32
+// granule counters at a time and expands the masks of the non-empty ones (512 bytes each).
+__global__ void __launch_bounds__(kThreads)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
   const uint64_t warp_global = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
@@ -206,16 +216,13 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
       todo &= todo - 1;
       const uint64_t g = g0 + src;
       const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
-      uint4 v[kRows];
-      uint32_t ext;
-      load_granule(a.buf, a.n, gran_off, lane, v, ext);
+      const uint4 mk = a.gran_mask[g * 32 + lane];
+      const uint32_t mask[kRows / 2] = {mk.x, mk.y, mk.z, mk.w};
       unsigned long long base = a.gran_prefix[g];
-      LaneResult r;
-      classify_granule<NS, true, false>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
       const uint64_t lane_off = gran_off + (uint64_t)lane * 16 - pat.anchor;
 #pragma unroll
       for (int u = 0; u < kRows; ++u) {
-        uint32_t m16 = (r.mask[u >> 1] >> (16 * (u & 1))) & 0xffffu;
+        uint32_t m16 = (mask[u >> 1] >> (16 * (u & 1))) & 0xffffu;
         const uint32_t cu = __popc(m16);
         if (!__any_sync(kFull, cu != 0)) continue;
         uint32_t inc = cu;  // inclusive warp scan of the per-lane counts of this row
@@ -239,45 +246,39 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
 }
 
 template <int NS>
-cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, cudaStream_t s) {
+cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
-  if (newlines) count_kernel<NS, true><<<grid, block, 0, s>>>(pat, a);
-  else count_kernel<NS, false><<<grid, block, 0, s>>>(pat, a);
-  return cudaGetLastError();
-}
-
-template <int NS>
-cudaError_t launch_emit_ns(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
-  const uint64_t blocks32 = div_up(a.n_tiles * kWarps, 32);          // units of 32 granules
-  const uint64_t want = (uint64_t)sm_count * 6;                        // persistent: a few CTAs per SM
-  const uint64_t need = div_up(blocks32, kWarps);
-  const dim3 grid((unsigned)(need < want ? need : want)), block(kThreads);
-  emit_kernel<NS><<<grid, block, 0, s>>>(pat, a);
+  if (masks) {
+    if (newlines) count_kernel<NS, true, true><<<grid, block, 0, s>>>(pat, a);
+    else count_kernel<NS, false, true><<<grid, block, 0, s>>>(pat, a);
+  } else {
+    if (newlines) count_kernel<NS, true, false><<<grid, block, 0, s>>>(pat, a);
+    else count_kernel<NS, false, false><<<grid, block, 0, s>>>(pat, a);
+  }
   return cudaGetLastError();
 }
 
 }  // namespace
 
-cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, cudaStream_t s) {
+cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
   switch (pat.m) {
-    case 1: return launch_count_ns<1>(pat, a, newlines, s);
-    case 2: return launch_count_ns<2>(pat, a, newlines, s);
-    case 3: return launch_count_ns<3>(pat, a, newlines, s);
-    case 4: return launch_count_ns<4>(pat, a, newlines, s);
-    default: return launch_count_ns<5>(pat, a, newlines, s);
+    case 1: return launch_count_ns<1>(pat, a, newlines, masks, s);
+    case 2: return launch_count_ns<2>(pat, a, newlines, masks, s);
+    case 3: return launch_count_ns<3>(pat, a, newlines, masks, s);
+    case 4: return launch_count_ns<4>(pat, a, newlines, masks, s);
+    default: return launch_count_ns<5>(pat, a, newlines, masks, s);
   }
 }
 
 cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
-  switch (pat.m) {
-    case 1: return launch_emit_ns<1>(pat, a, sm_count, s);
-    case 2: return launch_emit_ns<2>(pat, a, sm_count, s);
-    case 3: return launch_emit_ns<3>(pat, a, sm_count, s);
-    case 4: return launch_emit_ns<4>(pat, a, sm_count, s);
-    default: return launch_emit_ns<5>(pat, a, sm_count, s);
-  }
+  const uint64_t blocks32 = div_up(a.n_tiles * kWarps, 32);          // units of 32 granules
+  const uint64_t want = (uint64_t)sm_count * 8;                        // persistent: a few CTAs per SM
+  const uint64_t need = div_up(blocks32, kWarps);
+  const dim3 grid((unsigned)(need < want ? need : want)), block(kThreads);
+  emit_kernel<<<grid, block, 0, s>>>(pat, a);
+  return cudaGetLastError();
 }
 
 }  // namespace xsg

@@ -75,7 +75,8 @@ int xsg_init(int device, xsg_ctx** out) {
   if (!c) return XSG_ERR_NOMEM;
   c->device = device;
   XSG_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
-  XSG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  XSG_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
   XSG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
   for (auto& ev : c->ev) XSG_CUDA(cudaEventCreate(&ev));
   for (int i = 0; i < 2; ++i) {
@@ -100,7 +101,7 @@ void xsg_destroy(xsg_ctx* c) {
   cudaStreamSynchronize(c->stream);
   cudaStreamSynchronize(c->copy_stream);
   Scratch* all[] = {&c->gran_count, &c->gran_prefix, &c->nl_granule, &c->nl_prefix, &c->scan_tmp, &c->occ,
-                    &c->sel, &c->desc2, &c->stage[0], &c->stage[1], &c->seg_bounds};
+                    &c->sel, &c->desc2, &c->selq, &c->gran_mask, &c->stage[0], &c->stage[1], &c->seg_bounds};
   for (Scratch* s : all) s->release();
   for (auto& ev : c->ev) cudaEventDestroy(ev);
   for (int i = 0; i < 2; ++i) {
@@ -109,7 +110,7 @@ void xsg_destroy(xsg_ctx* c) {
   }
   cudaFree(c->d_scalars);
   cudaFreeHost(c->h_scalars);
-  cudaStreamDestroy(c->stream);
+  cudaStreamDestroy(c->own_stream);
   cudaStreamDestroy(c->copy_stream);
   delete c;
 }
@@ -121,6 +122,14 @@ int xsg_device_info(xsg_ctx* c, int* sm_count, uint64_t* total_mem, char* name, 
   if (sm_count) *sm_count = prop.multiProcessorCount;
   if (total_mem) *total_mem = prop.totalGlobalMem;
   if (name && name_cap) std::snprintf(name, name_cap, "%s", prop.name);
+  return XSG_OK;
+}
+
+int xsg_set_stream(xsg_ctx* c, void* cuda_stream) {
+  if (!c) return XSG_ERR_ARG;
+  XSG_CUDA(cudaSetDevice(c->device));
+  XSG_CUDA(cudaStreamSynchronize(c->stream));
+  c->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : c->own_stream;
   return XSG_OK;
 }
 

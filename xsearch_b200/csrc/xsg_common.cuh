@@ -34,13 +34,15 @@ struct ScanArgs {
   uint64_t n_tiles;          // CTAs of pass 1; n_tiles * kWarps granules
   uint32_t* gran_count;      // [granules] occurrences owned by each 4 KiB granule (ownership by anchor byte)
   uint32_t* nl_granule;      // [granules] '\n' per granule (newline mode) or nullptr
+  uint4* gran_mask;          // [granules x 32] occurrence bitmask (16 bits per lane and row) of every granule
+                             // with gran_count != 0, written by pass 1 and read by pass 2; nullptr = none
   const uint64_t* gran_prefix;  // [granules] exclusive prefix of gran_count (pass 2)
   uint64_t* occ;             // raw occurrence list (pass 2)
   uint64_t occ_cap;
 };
 
 // launchers implemented in scan_kernel.cu
-cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, cudaStream_t s);
+cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s);
 cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s);
 
 // ---- list-domain (post) kernels, list_kernels.cu -------------------------------------------
@@ -100,6 +102,9 @@ __device__ __forceinline__ uint32_t nonzero_lanes(uint32_t z) {
 // word-level "has a zero byte" predicate (non-zero result <=> some lane is zero); lanes above the
 // lowest zero lane may carry false flags, so use it only as a filter (2 instructions)
 __device__ __forceinline__ uint32_t haszero_filter(uint32_t z) { return (z - k01) & ~z; }
+
+// flags at bits 7/15/23/31 of f -> 4 bits in lane order
+__device__ __forceinline__ uint32_t nibble16(uint32_t f) { return (f * 0x00204081u) >> 28; }
 
 constexpr unsigned kFull = 0xffffffffu;
 constexpr unsigned long long kStatusShift = 62;

@@ -46,10 +46,11 @@ struct DevScalars {
 struct xsg_ctx {
   int device = 0;
   int sm_count = 0;
-  cudaStream_t stream = nullptr;       // compute
+  cudaStream_t stream = nullptr;       // compute (own_stream unless xsg_set_stream replaced it)
+  cudaStream_t own_stream = nullptr;
   cudaStream_t copy_stream = nullptr;  // H2D of streamed segments
   cudaEvent_t ev[6] = {};
-  xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2;
+  xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2, selq, gran_mask;
   xsg::Scratch stage[2];               // streamed segments (double buffer)
   xsg::Scratch seg_bounds;
   cudaEvent_t stage_copied[2] = {}, stage_free[2] = {};

@@ -138,7 +138,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
 
   if (count_only) {
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-    XSG_CUDA(launch_count(pat, a, false, s));
+    XSG_CUDA(launch_count(pat, a, false, false, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
     launch_reduce_u32(a.gran_count, n_gran, &ds->occ_total, s);
     launch_zone_count(buf, n, d_bounds, nb, pat, a.gran_count, &ds->zone_sub, &ds->zone_add, s);
@@ -157,10 +157,12 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       if ((rc = ctx->nl_prefix.reserve((n_gran + 1) * sizeof(uint64_t)))) return rc;
       a.nl_granule = ctx->nl_granule.as<uint32_t>();
     }
+    if ((rc = ctx->gran_mask.reserve(n_gran * 32 * sizeof(uint4)))) return rc;
+    a.gran_mask = ctx->gran_mask.as<uint4>();
     a.gran_prefix = ctx->gran_prefix.as<uint64_t>();
     // pass 1: every byte once -> granule counters; then their exclusive prefix
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
-    XSG_CUDA(launch_count(pat, a, want_idx, s));
+    XSG_CUDA(launch_count(pat, a, want_idx, true, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
     launch_exscan_u32(a.gran_count, n_gran, ctx->gran_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
                       &ds->occ_total, s);
@@ -229,6 +231,10 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
             c.out_line_start = part->line_start;
             c.out_line_len = part->line_len;
           }
+          if (c.out_line_off || c.out_line_idx || c.out_line_start) {
+            if ((rc = ctx->selq.reserve(k * sizeof(uint64_t)))) return rc;
+            c.selq = ctx->selq.as<uint64_t>();
+          }
         }
         c.desc = ctx->desc2.as<unsigned long long>();
         c.ticket = &ds->ticket[1 + fam];
@@ -237,7 +243,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         XSG_CUDA(cudaMemsetAsync(c.desc, 0, n_ct * sizeof(unsigned long long), s));
         launch_compact(c, pat, s);
         XSG_CUDA(cudaGetLastError());
-        st->launches += 1;
+        st->launches += c.selq ? 2 : 1;
       }
     }
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
