@@ -3,8 +3,13 @@
 // exact restatement of the reference's per-chunk result semantics (search_wrappers.h:36-50,
 // 111-123,149-154,163-207) including the scalar-tail quirk of simd::strstr
 // (simd_search.cpp:58-78,169-171,203) -- see SURVEY.md 3.3 for the model.
+#include <cooperative_groups.h>
+#include <cooperative_groups/reduce.h>
+
 #include "corpus_gen.h"
 #include "list_kernels.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace xsg {
 
@@ -120,22 +125,38 @@ __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t* total) {
   return r;
 }
 
-__global__ void __launch_bounds__(kScanThreads) exscan_sums_kernel(const uint32_t* __restrict__ in, uint64_t n,
+// The scans below handle up to two u32 tables of the same length in one set of launches (blockIdx.y
+// selects the table): granule occurrence counts and granule newline counts.
+struct Scan2 {
+  const uint32_t* in[2];
+  uint64_t* out[2];
+  unsigned long long* total[2];
+};
+
+__global__ void __launch_bounds__(kScanThreads) exscan_sums_kernel(const __grid_constant__ Scan2 a, uint64_t n,
                                                                    uint64_t* tmp) {
+  const uint32_t* __restrict__ in = a.in[blockIdx.y];
   const uint64_t base = (uint64_t)blockIdx.x * kScanTile + (uint64_t)threadIdx.x * kScanItems;
   uint32_t v = 0;
+  if (base + kScanItems <= n) {
+    const uint4 x = *reinterpret_cast<const uint4*>(in + base), y = *reinterpret_cast<const uint4*>(in + base + 4);
+    v = x.x + x.y + x.z + x.w + y.x + y.y + y.z + y.w;
+  } else {
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i)
-    if (base + i < n) v += in[base + i];
+    for (int i = 0; i < kScanItems; ++i)
+      if (base + i < n) v += in[base + i];
+  }
   uint32_t total;
   block_exscan(v, &total);
-  if (threadIdx.x == 0) tmp[blockIdx.x] = total;
+  if (threadIdx.x == 0) tmp[(uint64_t)blockIdx.y * gridDim.x + blockIdx.x] = total;
 }
 
-// single block: exclusive scan of tmp[0..nblk) in place, total -> *total
-__global__ void __launch_bounds__(1024) exscan_top_kernel(uint64_t* tmp, uint64_t nblk, unsigned long long* total) {
+// one block per table: exclusive scan of tmp[y * nblk .. (y + 1) * nblk) in place, total -> *total[y]
+__global__ void __launch_bounds__(1024) exscan_top_kernel(const __grid_constant__ Scan2 a, uint64_t* tmp_all,
+                                                          uint64_t nblk) {
   __shared__ unsigned long long s_w[32];
   __shared__ unsigned long long s_carry;
+  uint64_t* tmp = tmp_all + (uint64_t)blockIdx.x * nblk;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
@@ -168,25 +189,46 @@ __global__ void __launch_bounds__(1024) exscan_top_kernel(uint64_t* tmp, uint64_
     if (threadIdx.x == 1023) s_carry = ex + v;
     __syncthreads();
   }
-  if (threadIdx.x == 0) *total = s_carry;
+  if (threadIdx.x == 0) *a.total[blockIdx.x] = s_carry;
 }
 
-__global__ void __launch_bounds__(kScanThreads) exscan_apply_kernel(const uint32_t* __restrict__ in, uint64_t n,
-                                                                    const uint64_t* __restrict__ tmp, uint64_t* out) {
+__global__ void __launch_bounds__(kScanThreads) exscan_apply_kernel(const __grid_constant__ Scan2 a, uint64_t n,
+                                                                    const uint64_t* __restrict__ tmp) {
+  const uint32_t* __restrict__ in = a.in[blockIdx.y];
+  uint64_t* __restrict__ out = a.out[blockIdx.y];
   const uint64_t base = (uint64_t)blockIdx.x * kScanTile + (uint64_t)threadIdx.x * kScanItems;
   uint32_t x[kScanItems];
   uint32_t v = 0;
+  const bool full = base + kScanItems <= n;
+  if (full) {
+    const uint4 p = *reinterpret_cast<const uint4*>(in + base), q = *reinterpret_cast<const uint4*>(in + base + 4);
+    x[0] = p.x; x[1] = p.y; x[2] = p.z; x[3] = p.w; x[4] = q.x; x[5] = q.y; x[6] = q.z; x[7] = q.w;
+  } else {
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i) {
-    x[i] = base + i < n ? in[base + i] : 0;
-    v += x[i];
+    for (int i = 0; i < kScanItems; ++i) x[i] = base + i < n ? in[base + i] : 0;
   }
-  uint32_t total;
-  uint64_t run = tmp[blockIdx.x] + block_exscan(v, &total);
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i) {
-    if (base + i < n) out[base + i] = run;
-    run += x[i];
+  for (int i = 0; i < kScanItems; ++i) v += x[i];
+  uint32_t total;
+  uint64_t run = tmp[(uint64_t)blockIdx.y * gridDim.x + blockIdx.x] + block_exscan(v, &total);
+  if (full) {
+    uint64_t r[kScanItems];
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      r[i] = run;
+      run += x[i];
+    }
+    ulonglong2* o = reinterpret_cast<ulonglong2*>(out + base);
+#pragma unroll
+    for (int i = 0; i < kScanItems / 2; ++i) o[i] = make_ulonglong2(r[2 * i], r[2 * i + 1]);
+    if (base + kScanItems == n) out[n] = run;
+  } else {
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+      if (base + i < n) out[base + i] = run;
+      run += x[i];
+    }
+    if (base < n) out[n] = run;  // only the thread that holds the ragged end gets here
   }
 }
 
@@ -232,13 +274,17 @@ void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, 
   reduce_u32_kernel<<<grid, 256, 0, s>>>(in, n, out);
 }
 
-void launch_exscan_u32(const uint32_t* in, uint64_t n, uint64_t* out, uint64_t* tmp, unsigned long long* total,
-                       cudaStream_t s) {
+void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
+                        uint64_t* out_b, unsigned long long* total_b, uint64_t n, uint64_t* tmp, cudaStream_t s) {
   if (n == 0) return;
   const uint64_t nblk = div_up(n, kScanTile);
-  exscan_sums_kernel<<<(unsigned)nblk, kScanThreads, 0, s>>>(in, n, tmp);
-  exscan_top_kernel<<<1, 1024, 0, s>>>(tmp, nblk, total);
-  exscan_apply_kernel<<<(unsigned)nblk, kScanThreads, 0, s>>>(in, n, tmp, out);
+  Scan2 a{};
+  a.in[0] = in_a; a.out[0] = out_a; a.total[0] = total_a;
+  a.in[1] = in_b; a.out[1] = out_b; a.total[1] = total_b;
+  const unsigned tables = in_b ? 2 : 1;
+  exscan_sums_kernel<<<dim3((unsigned)nblk, tables), kScanThreads, 0, s>>>(a, n, tmp);
+  exscan_top_kernel<<<tables, 1024, 0, s>>>(a, tmp, nblk);
+  exscan_apply_kernel<<<dim3((unsigned)nblk, tables), kScanThreads, 0, s>>>(a, n, tmp);
 }
 
 }  // namespace xsg

@@ -22,9 +22,11 @@ void launch_check_bounds(const uint8_t* buf, uint64_t n, const uint64_t* bounds,
 
 // sum of a u32 array into *out (out must be zero before)
 void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, cudaStream_t s);
-// exclusive scan u32 -> u64 (out[i] = sum in[0..i)), *total = sum; tmp holds div_up(n, 2048) u64
-void launch_exscan_u32(const uint32_t* in, uint64_t n, uint64_t* out, uint64_t* tmp, unsigned long long* total,
-                       cudaStream_t s);
+// exclusive scans u32 -> u64 of one or two tables of n entries in the same three launches
+// (out[i] = sum in[0..i), out[n] = *total = sum); in_b may be nullptr; tmp holds 2 * div_up(n, 2048) u64.
+// The tables must be 16-byte aligned.
+void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
+                        uint64_t* out_b, unsigned long long* total_b, uint64_t n, uint64_t* tmp, cudaStream_t s);
 
 // selection flags of the non-zone part of every chunk
 void launch_select(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);

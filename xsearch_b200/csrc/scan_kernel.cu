@@ -204,10 +204,10 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
 __global__ void __launch_bounds__(kThreads)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
-  const uint64_t warp_global = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
-  const uint64_t total_warps = (uint64_t)gridDim.x * kWarps;
   const uint64_t n_gran = a.n_tiles * kWarps;
-  for (uint64_t g0 = warp_global * 32; g0 < n_gran; g0 += total_warps * 32) {
+  {  // one warp per unit of 32 granules: the serial part of a warp is the handful of hit granules of its unit
+    const uint64_t g0 = ((uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5)) * 32;
+    if (g0 >= n_gran) return;
     const uint64_t gi = g0 + lane;
     const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
     unsigned todo = __ballot_sync(kFull, c != 0);
@@ -273,10 +273,9 @@ cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, b
 
 cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
-  const uint64_t blocks32 = div_up(a.n_tiles * kWarps, 32);          // units of 32 granules
-  const uint64_t want = (uint64_t)sm_count * 8;                        // persistent: a few CTAs per SM
-  const uint64_t need = div_up(blocks32, kWarps);
-  const dim3 grid((unsigned)(need < want ? need : want)), block(kThreads);
+  (void)sm_count;
+  const uint64_t units = div_up(a.n_tiles * kWarps, 32);  // units of 32 granules, one warp each
+  const dim3 grid((unsigned)div_up(units, kWarps)), block(kThreads);
   emit_kernel<<<grid, block, 0, s>>>(pat, a);
   return cudaGetLastError();
 }

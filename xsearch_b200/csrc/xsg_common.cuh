@@ -54,6 +54,8 @@ struct ListArgs {
   const uint64_t* occ;     // sorted raw occurrences
   uint64_t k;              // number of raw occurrences
   uint8_t* sel;            // [k] selection flags (output of select / zone kernels)
+  const uint64_t* gran_prefix;  // [n_gran + 1] exclusive prefix of the granule counts (brackets searches in occ) or nullptr
+  uint64_t n_gran;
 };
 
 // small helpers usable from host code

@@ -150,11 +150,11 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     st->raw += h.occ_total;
     part->n_match = h.occ_total - h.zone_sub + h.zone_add;
   } else {
-    if ((rc = ctx->gran_prefix.reserve((n_gran + 1) * sizeof(uint64_t)))) return rc;
-    if ((rc = ctx->scan_tmp.reserve((div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
+    if ((rc = ctx->gran_prefix.reserve((n_gran + 2) * sizeof(uint64_t)))) return rc;
+    if ((rc = ctx->scan_tmp.reserve(2 * (div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
     if (want_idx) {
       if ((rc = ctx->nl_granule.reserve(n_gran * sizeof(uint32_t)))) return rc;
-      if ((rc = ctx->nl_prefix.reserve((n_gran + 1) * sizeof(uint64_t)))) return rc;
+      if ((rc = ctx->nl_prefix.reserve((n_gran + 2) * sizeof(uint64_t)))) return rc;
       a.nl_granule = ctx->nl_granule.as<uint32_t>();
     }
     if ((rc = ctx->gran_mask.reserve(n_gran * 32 * sizeof(uint4)))) return rc;
@@ -164,42 +164,41 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
     XSG_CUDA(launch_count(pat, a, want_idx, true, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
-    launch_exscan_u32(a.gran_count, n_gran, ctx->gran_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
-                      &ds->occ_total, s);
+    // one set of launches scans both tables: granule occurrence counts and granule newline counts
+    launch_exscan2_u32(a.gran_count, ctx->gran_prefix.as<uint64_t>(), &ds->occ_total, a.nl_granule,
+                       want_idx ? ctx->nl_prefix.as<uint64_t>() : nullptr, &ds->nl_total, n_gran,
+                       ctx->scan_tmp.as<uint64_t>(), s);
     XSG_CUDA(cudaGetLastError());
     st->launches += 4;
     // pass 2: positions of the occurrences (re-reads only granules that hold any)
     uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
     if (ctx->occ.cap / sizeof(uint64_t) > cap && !occ_cap_opt) cap = ctx->occ.cap / sizeof(uint64_t);
-    uint64_t k = 0;
-    for (int attempt = 0;; ++attempt) {
-      if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
+    // the host needs the number of occurrences (allocation sizes, grids); it travels while pass 2 runs
+    XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
+                             cudaMemcpyDeviceToHost, s));
+    XSG_CUDA(cudaEventRecord(ctx->ev[4], s));
+    if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
+    a.occ = ctx->occ.as<uint64_t>();
+    a.occ_cap = cap;
+    XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+    st->launches += 1;
+    XSG_CUDA(cudaEventSynchronize(ctx->ev[4]));
+    const uint64_t k = ctx->h_scalars->occ_total;
+    if (k > cap) {  // rare: denser than the estimate -> emit again with the exact capacity
+      XSG_CUDA(cudaStreamSynchronize(s));
+      if ((rc = ctx->occ.reserve(k * sizeof(uint64_t)))) return rc;
       a.occ = ctx->occ.as<uint64_t>();
-      a.occ_cap = cap;
+      a.occ_cap = k;
       XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
       st->launches += 1;
-      XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
-                               cudaMemcpyDeviceToHost, s));
-      XSG_CUDA(cudaStreamSynchronize(s));
-      k = ctx->h_scalars->occ_total;
-      if (k <= cap) break;
-      if (attempt > 0) {
-        set_error("occurrence buffer overflow after retry");
-        return XSG_ERR_STATE;
-      }
-      cap = k;  // rare: denser than the estimate -> emit again with the exact capacity
     }
     st->raw += k;
-    if (want_idx) {
-      launch_exscan_u32(a.nl_granule, n_gran, ctx->nl_prefix.as<uint64_t>(), ctx->scan_tmp.as<uint64_t>(),
-                        &ds->nl_total, s);
-      st->launches += 3;
-    }
     if (k > 0) {
       if ((rc = ctx->sel.reserve(k))) return rc;
       const uint64_t n_ct = div_up(k, 2048);
       if ((rc = ctx->desc2.reserve(n_ct * sizeof(unsigned long long)))) return rc;
-      ListArgs l{buf, n, d_bounds, nb, ctx->occ.as<uint64_t>(), k, ctx->sel.as<uint8_t>()};
+      ListArgs l{buf, n, d_bounds, nb, ctx->occ.as<uint64_t>(), k, ctx->sel.as<uint8_t>(),
+                 ctx->gran_prefix.as<uint64_t>(), n_gran};
       for (int fam = 0; fam < 2; ++fam) {
         if (fam == 0 ? !want_match : !want_line) continue;
         const int mode = fam == 1 ? kSelLine : (pat.bordered ? kSelMatchBordered : kSelMatch);
