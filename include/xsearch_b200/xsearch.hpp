@@ -1,0 +1,598 @@
+// xsearch.hpp -- the reference's one-call API on top of the B200 C ABI (C++20, header-only).
+//
+//   auto s = xs::extern_search<xs::lines>(pattern, file, meta_file, num_threads, max_num_readers);
+//   for (auto const& line : *s->getResult()) ...      // live: blocks until more results or closed
+//   s->join();  s->getResult()->size();  s->getResult()->copyResultSafe();
+//
+// Shapes kept from the reference (file:line in /root/reference):
+//   * extern_search<Tag>(pattern, file, meta_file, num_threads, max_num_readers)     README.md:72, checkit.cpp:4
+//     and the overloads (pattern, file, ignore_case, num_threads)                    README.md:37, example/grep.cpp:69-77
+//     / (pattern, file, meta_file, ignore_case, num_threads, max_num_readers)        test/src/xsearchTest.cpp:1227-1228
+//   * tags count (alias count_matches), count_lines, match_byte_offsets, line_byte_offsets,
+//     line_indices, lines                                                             README.md:72-81
+//   * Searcher: work starts in the constructor, join() idempotent, destructor joins,
+//     non-copyable / non-movable                                                      include/xsearch/Searcher.h:41-59
+//   * Result: add / close / size / begin / end with an iterator whose operator!= blocks until more data
+//     or close                                                                        include/xsearch/ResultTypes.h:31-130
+//     count tags yield running totals, the last one is the total                      test/src/xsearchTest.cpp:735-739
+//
+// What runs underneath is NOT the reference's thread pool: max_num_readers reader threads pread the file
+// into pinned segments, one pusher thread hands them to libxsg.so (xsg_stream_push: H2D copy overlapped
+// with the scan of the previous segment on the GPU) and publishes the result parts in file order.
+// There is no CPU search path: without a CUDA device extern_search throws.
+#pragma once
+
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdint>
+#include <cstring>
+#include <deque>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <type_traits>
+#include <vector>
+
+#include "../xsg.h"
+#include "metafile.hpp"
+
+namespace xs {
+
+// ---- tags ------------------------------------------------------------------------------------------
+struct count {
+  using value_type = uint64_t;
+  static constexpr uint32_t kind = XSG_COUNT;
+  static constexpr bool is_count = true;
+};
+using count_matches = count;  // spelling used by the reference's tests (xsearchTest.cpp:344)
+struct count_lines {
+  using value_type = uint64_t;
+  static constexpr uint32_t kind = XSG_COUNT_LINES;
+  static constexpr bool is_count = true;
+};
+struct match_byte_offsets {
+  using value_type = uint64_t;
+  static constexpr uint32_t kind = XSG_MATCH_BYTE_OFFSETS;
+  static constexpr bool is_count = false;
+};
+struct line_byte_offsets {
+  using value_type = uint64_t;
+  static constexpr uint32_t kind = XSG_LINE_BYTE_OFFSETS;
+  static constexpr bool is_count = false;
+};
+struct line_indices {
+  using value_type = uint64_t;
+  static constexpr uint32_t kind = XSG_LINE_INDICES;
+  static constexpr bool is_count = false;
+};
+struct lines {
+  using value_type = std::string;
+  static constexpr uint32_t kind = XSG_LINES;
+  static constexpr bool is_count = false;
+};
+
+// knobs the reference does not have (device selection, chunking); defaults reproduce v1 chunking
+struct Options {
+  int device = 0;
+  uint64_t min_chunk = XSG_DEFAULT_MIN_CHUNK;   // v1: chunks of >= 16 MiB, extended through the next '\n'
+  uint64_t segment_bytes = 256ull << 20;        // bytes read / copied / scanned per pipeline step
+};
+
+// ---- result collector ------------------------------------------------------------------------------
+// Flat, ordered collection of result elements with the reference's blocking-iterator behaviour.
+// For count tags the elements are running totals and size() is the total.
+template <class T>
+class Result {
+ public:
+  class iterator {
+   public:
+    explicit iterator(Result* r) : _r(r) {}
+    iterator& operator++() {
+      ++_i;
+      return *this;
+    }
+    const T& operator*() const {
+      std::unique_lock lock(_r->_m);
+      return _r->_data[_i];
+    }
+    // blocks until element _i exists or the result is closed (ResultTypes.h:48-60)
+    bool operator!=(const iterator&) const {
+      std::unique_lock lock(_r->_m);
+      _r->_cv.wait(lock, [&] { return _i < _r->_data.size() || _r->_closed; });
+      return _i < _r->_data.size();
+    }
+    bool operator==(const iterator& o) const { return !(*this != o); }
+
+   private:
+    Result* _r;
+    size_t _i = 0;
+  };
+
+  explicit Result(bool counting) : _counting(counting) {}
+  Result(const Result&) = delete;
+  Result& operator=(const Result&) = delete;
+
+  // producer side ----------------------------------------------------------------------------------
+  bool add(std::vector<T>&& part) {
+    std::unique_lock lock(_m);
+    if (_closed) return false;
+    for (auto& v : part) _data.push_back(std::move(v));
+    _cv.notify_all();
+    return true;
+  }
+  void close() {
+    {
+      std::unique_lock lock(_m);
+      _closed = true;
+    }
+    _cv.notify_all();
+  }
+
+  // consumer side ----------------------------------------------------------------------------------
+  // count tags: the count so far (the total once closed); vector tags: number of elements so far
+  size_t size() const {
+    std::unique_lock lock(_m);
+    if constexpr (std::is_same_v<T, uint64_t>) {
+      if (_counting) return _data.empty() ? 0 : static_cast<size_t>(_data.back());
+    }
+    return _data.size();
+  }
+  bool empty() const { return size() == 0; }
+  bool is_closed() const {
+    std::unique_lock lock(_m);
+    return _closed;
+  }
+  void wait_closed() const {
+    std::unique_lock lock(_m);
+    _cv.wait(lock, [&] { return _closed; });
+  }
+  std::vector<T> copyResultSafe() const {
+    std::unique_lock lock(_m);
+    return std::vector<T>(_data.begin(), _data.end());
+  }
+  T at(size_t i) const {
+    std::unique_lock lock(_m);
+    return _data.at(i);
+  }
+  T operator[](size_t i) const { return at(i); }
+  iterator begin() { return iterator(this); }
+  iterator end() { return iterator(this); }
+
+ private:
+  const bool _counting;
+  mutable std::mutex _m;
+  mutable std::condition_variable _cv;
+  std::deque<T> _data;  // deque: references handed out by the iterator survive later push_backs
+  bool _closed = false;
+};
+
+// ---- searcher ----------------------------------------------------------------------------------------
+namespace detail {
+
+inline std::string last_error(const char* what) { return std::string(what) + ": " + xsg_last_error(); }
+
+struct Pinned {  // one pinned host buffer (cudaHostAlloc through the C ABI)
+  uint8_t* p = nullptr;
+  size_t cap = 0;
+  Pinned() = default;
+  Pinned(const Pinned&) = delete;
+  Pinned& operator=(const Pinned&) = delete;
+  ~Pinned() { release(); }
+  bool alloc(size_t n) {
+    release();
+    void* q = nullptr;
+    if (xsg_host_alloc(n, &q) != XSG_OK) return false;
+    p = static_cast<uint8_t*>(q);
+    cap = n;
+    return true;
+  }
+  void release() {
+    if (p) xsg_host_free(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct Block {  // one unit of reading: a byte range of the file
+  uint64_t off = 0, len = 0;
+  std::vector<uint64_t> rel_bounds;  // meta-file mode: chunk ends relative to off
+};
+
+}  // namespace detail
+
+template <class Tag>
+class Searcher {
+ public:
+  using value_type = typename Tag::value_type;
+  using ResultT = Result<value_type>;
+
+  Searcher(std::string pattern, const std::string& file_path, const std::string& meta_file_path, int num_threads,
+           int max_num_readers, Options opt = {})
+      : _pattern(std::move(pattern)), _opt(opt), _result(Tag::is_count) {
+    if (_pattern.empty() || _pattern.size() > XSG_MAX_PATTERN || _pattern.find('\n') != std::string::npos)
+      throw std::invalid_argument("xs::extern_search: the GPU literal path needs a pattern of 1..64 bytes without '\\n'");
+    _num_threads = num_threads < 1 ? 1 : num_threads;  // accepted for API compatibility; the search itself runs on the GPU
+    _num_readers = max_num_readers < 1 ? 1 : max_num_readers;
+    if (_opt.min_chunk == 0) _opt.min_chunk = XSG_DEFAULT_MIN_CHUNK;
+    if (_opt.segment_bytes < 2 * _opt.min_chunk) _opt.segment_bytes = 2 * _opt.min_chunk;
+    _fd = ::open(file_path.c_str(), O_RDONLY);
+    if (_fd < 0) throw std::runtime_error("xs::extern_search: cannot open '" + file_path + "'");
+    struct stat sb;
+    if (::fstat(_fd, &sb) != 0 || !S_ISREG(sb.st_mode)) {
+      ::close(_fd);
+      throw std::runtime_error("xs::extern_search: '" + file_path + "' is not a regular file");
+    }
+    _size = static_cast<uint64_t>(sb.st_size);
+    try {
+      plan(meta_file_path);
+      if (xsg_init(_opt.device, &_ctx) != XSG_OK) throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init"));
+      if (xsg_stream_open(_ctx, reinterpret_cast<const uint8_t*>(_pattern.data()), static_cast<uint32_t>(_pattern.size()),
+                          Tag::kind, nullptr, &_stream) != XSG_OK)
+        throw std::runtime_error(detail::last_error("xs::extern_search: xsg_stream_open"));
+    } catch (...) {
+      if (_ctx) xsg_destroy(_ctx);
+      ::close(_fd);
+      throw;
+    }
+    _running.store(true);
+    _pusher = std::thread(&Searcher::run_pusher, this);
+  }
+
+  ~Searcher() {
+    join();
+    if (_stream) xsg_stream_abort(_stream);
+    _bufs.clear();
+    if (_ctx) xsg_destroy(_ctx);
+    if (_fd >= 0) ::close(_fd);
+  }
+
+  Searcher(Searcher&&) = delete;
+  Searcher(const Searcher&) = delete;
+  Searcher& operator=(Searcher&&) = delete;
+  Searcher& operator=(const Searcher&) = delete;
+
+  // block until the search has finished (idempotent; Searcher.h:52-59)
+  void join() {
+    std::unique_lock lock(_join_m);
+    if (_pusher.joinable()) _pusher.join();
+    _running.store(false);
+  }
+  [[nodiscard]] bool running() const { return _running.load(); }
+  ResultT* getResult() { return &_result; }
+  // nothing throws after extern_search returned: a failure closes the result early and is reported here
+  [[nodiscard]] bool ok() const { return !_failed.load(); }
+  std::string error() const {
+    std::unique_lock lock(_m);
+    return _error;
+  }
+  // device time of all scans / wall time of the streamed pipeline (valid after join())
+  xsg_timings timings() const { return _timings; }
+  uint64_t bytes() const { return _size; }
+
+ private:
+  // ---- planning: which byte ranges are read as one block --------------------------------------------
+  void plan(const std::string& meta_file_path) {
+    if (!meta_file_path.empty()) {
+      MetaFile mf(meta_file_path);
+      if (mf.compression_type() != CompressionType::NONE)
+        throw std::runtime_error("xs::extern_search: compressed inputs are outside the GPU path (decompress first)");
+      if (mf.original_size() != _size) throw std::runtime_error("xs::extern_search: the meta file does not describe this file");
+      _meta_mode = true;
+      const std::vector<uint64_t> b = mf.chunk_bounds();
+      for (size_t c0 = 0; c0 < b.size();) {
+        const uint64_t b0 = c0 ? b[c0 - 1] : 0;
+        size_t c1 = c0 + 1;
+        while (c1 < b.size() && b[c1] - b0 <= _opt.segment_bytes) ++c1;
+        detail::Block blk;
+        blk.off = b0;
+        blk.len = b[c1 - 1] - b0;
+        for (size_t c = c0; c < c1; ++c) blk.rel_bounds.push_back(b[c] - b0);
+        _max_block = std::max<uint64_t>(_max_block, blk.len);
+        _blocks.push_back(std::move(blk));
+        c0 = c1;
+      }
+      _headroom = 0;
+    } else {
+      for (uint64_t off = 0; off < _size; off += _opt.segment_bytes) {
+        detail::Block blk;
+        blk.off = off;
+        blk.len = std::min<uint64_t>(_opt.segment_bytes, _size - off);
+        _max_block = std::max<uint64_t>(_max_block, blk.len);
+        _blocks.push_back(std::move(blk));
+      }
+      // the unfinished last chunk of a block (< min_chunk + one line) is carried into the next buffer
+      _headroom = _opt.min_chunk + (1u << 20);
+    }
+  }
+
+  void fail(const std::string& msg) {
+    {
+      std::unique_lock lock(_m);
+      if (_error.empty()) _error = msg;
+    }
+    _failed.store(true);
+    _cv.notify_all();
+  }
+
+  // ---- reader threads: pread blocks into free pinned buffers, in block order ---------------------------
+  void run_reader() {
+    for (;;) {
+      int buf;
+      size_t i;
+      {
+        // a buffer is taken BEFORE the block index, so block i always owns a buffer before block i + 1
+        std::unique_lock lock(_m);
+        _cv.wait(lock, [&] { return !_free.empty() || _failed.load() || _next_block >= _blocks.size(); });
+        if (_failed.load() || _next_block >= _blocks.size()) return;
+        buf = _free.back();
+        _free.pop_back();
+        i = _next_block++;
+      }
+      const detail::Block& b = _blocks[i];
+      uint8_t* dst = _bufs[buf]->p + _headroom;
+      uint64_t done = 0;
+      while (done < b.len) {
+        const ssize_t r = ::pread(_fd, dst + done, static_cast<size_t>(std::min<uint64_t>(b.len - done, 1u << 30)),
+                                  static_cast<off_t>(b.off + done));
+        if (r <= 0) {
+          fail("xs::extern_search: read error (file truncated while searching?)");
+          return;
+        }
+        done += static_cast<uint64_t>(r);
+      }
+      {
+        std::unique_lock lock(_m);
+        _ready[i] = buf;
+      }
+      _cv.notify_all();
+    }
+  }
+
+  void give_back(int buf) {
+    if (buf < 0) return;
+    {
+      std::unique_lock lock(_m);
+      _free.push_back(buf);
+    }
+    _cv.notify_all();
+  }
+
+  // a pushed segment whose results have not been collected yet
+  struct Inflight {
+    bool valid = false;
+    int buf = -1;                           // pool buffer holding its bytes
+    std::unique_ptr<detail::Pinned> extra;  // or a one-off buffer (a carry longer than the headroom)
+    const uint8_t* ptr = nullptr;           // first byte of the segment on the host
+    uint64_t goff = 0;                      // its global file offset
+  };
+
+  // ---- results of one finished part -> the result collector ------------------------------------------
+  bool harvest(const xsg_result* res, uint64_t part, const Inflight& seg) {
+    const uint64_t n = xsg_result_part_count(res, part, Tag::kind);
+    if constexpr (Tag::is_count) {
+      _running_total += n;
+      _result.add(std::vector<uint64_t>{_running_total});
+      _published = true;
+    } else if constexpr (std::is_same_v<value_type, uint64_t>) {
+      std::vector<uint64_t> v(n);
+      if (n && xsg_result_part_copy(res, part, Tag::kind, v.data(), n) != XSG_OK) return false;
+      _result.add(std::move(v));
+    } else {
+      std::vector<uint64_t> st(n), ln(n);
+      if (n && (xsg_result_part_copy(res, part, XSG_LINES, st.data(), n) != XSG_OK ||
+                xsg_result_part_copy_line_lengths(res, part, ln.data(), n) != XSG_OK))
+        return false;
+      std::vector<std::string> out;
+      out.reserve(n);
+      for (uint64_t i = 0; i < n; ++i)
+        out.emplace_back(reinterpret_cast<const char*>(seg.ptr) + (st[i] - seg.goff), static_cast<size_t>(ln[i]));
+      _result.add(std::move(out));
+    }
+    return true;
+  }
+
+  void release(Inflight& s) {
+    give_back(s.buf);
+    s = Inflight();
+  }
+
+  // ---- pusher thread: forms segments of whole reference chunks and drives the GPU -------------------
+  void run_pusher() {
+    try {
+      pusher_body();
+    } catch (const std::exception& e) {
+      fail(e.what());
+    }
+    // wake and collect the readers, then close the result (the reference closes when the last worker ends)
+    {
+      std::unique_lock lock(_m);
+      _next_block = _blocks.size();
+    }
+    _cv.notify_all();
+    for (auto& t : _readers)
+      if (t.joinable()) t.join();
+    _result.close();
+  }
+
+  void pusher_body() {
+    const size_t nbuf = static_cast<size_t>(_num_readers) + 2;
+    for (size_t i = 0; i < nbuf && i < _blocks.size() + 1 && !_blocks.empty(); ++i) {
+      auto b = std::make_unique<detail::Pinned>();
+      if (!b->alloc(static_cast<size_t>(_headroom + _max_block + 64))) throw std::runtime_error(detail::last_error("pinned buffer"));
+      _bufs.push_back(std::move(b));
+      _free.push_back(static_cast<int>(i));
+    }
+    _ready.assign(_blocks.size(), -1);
+    for (int t = 0; t < _num_readers; ++t) _readers.emplace_back(&Searcher::run_reader, this);
+
+    Inflight prev;          // pushed, results not collected yet
+    Inflight carry_holder;  // holds the bytes of `carry` when they belong to a segment that was not pushed
+    const uint8_t* carry = nullptr;
+    uint64_t carry_len = 0;
+    uint64_t parts_done = 0;
+    std::vector<uint64_t> bounds;
+
+    for (size_t i = 0; i < _blocks.size(); ++i) {
+      int buf;
+      {
+        std::unique_lock lock(_m);
+        _cv.wait(lock, [&] { return _ready[i] >= 0 || _failed.load(); });
+        if (_failed.load()) throw std::runtime_error(_error);
+        buf = _ready[i];
+      }
+      const detail::Block& b = _blocks[i];
+      Inflight cur;
+      cur.valid = true;
+      cur.buf = buf;
+      uint64_t seg_len;
+      if (carry_len <= _headroom) {
+        cur.ptr = _bufs[buf]->p + _headroom - carry_len;
+        if (carry_len) std::memcpy(const_cast<uint8_t*>(cur.ptr), carry, carry_len);
+      } else {  // a line (or unfinished chunk) longer than the headroom: one-off buffer
+        cur.extra = std::make_unique<detail::Pinned>();
+        if (!cur.extra->alloc(static_cast<size_t>(carry_len + b.len + 64))) throw std::runtime_error(detail::last_error("pinned buffer"));
+        std::memcpy(cur.extra->p, carry, carry_len);
+        std::memcpy(cur.extra->p + carry_len, _bufs[buf]->p + _headroom, b.len);
+        cur.ptr = cur.extra->p;
+        give_back(buf);
+        cur.buf = -1;
+      }
+      seg_len = carry_len + b.len;
+      cur.goff = b.off - carry_len;
+      if (carry_holder.valid) release(carry_holder);  // its bytes have been copied
+
+      // chunk bounds of this segment
+      uint64_t consumed;
+      const bool eof = i + 1 == _blocks.size();
+      if (_meta_mode) {
+        bounds = b.rel_bounds;
+        consumed = seg_len;
+      } else {
+        bounds.clear();
+        uint64_t pos = 0;
+        while (seg_len - pos >= _opt.min_chunk) {  // v1 rule: >= min_chunk bytes, then through the next '\n'
+          const uint64_t from = pos + _opt.min_chunk - 1;
+          const void* nl = std::memchr(cur.ptr + from, '\n', static_cast<size_t>(seg_len - from));
+          if (!nl) break;
+          pos = static_cast<uint64_t>(static_cast<const uint8_t*>(nl) - cur.ptr) + 1;
+          bounds.push_back(pos);
+        }
+        if (eof && pos < seg_len) {
+          pos = seg_len;
+          bounds.push_back(pos);
+        }
+        consumed = pos;
+      }
+      carry = cur.ptr + consumed;
+      carry_len = seg_len - consumed;
+      if (bounds.empty()) {  // nothing complete yet: everything is carried on
+        carry_holder = std::move(cur);
+        continue;
+      }
+      if (xsg_stream_push(_stream, cur.ptr, consumed, bounds.data(), bounds.size(), nullptr) != XSG_OK)
+        throw std::runtime_error(detail::last_error("xsg_stream_push"));
+      // the previous segment was scanned inside this push: publish its results, free its buffer
+      const xsg_result* res = xsg_stream_result(_stream);
+      while (parts_done < xsg_result_num_parts(res)) {
+        if (!harvest(res, parts_done, prev)) throw std::runtime_error(detail::last_error("result copy"));
+        ++parts_done;
+      }
+      if (prev.valid) release(prev);
+      prev = std::move(cur);
+    }
+    xsg_result* fin = nullptr;
+    xsg_stream* st = _stream;
+    _stream = nullptr;  // close destroys it whatever happens
+    if (xsg_stream_close(st, &fin) != XSG_OK) throw std::runtime_error(detail::last_error("xsg_stream_close"));
+    bool ok = true;
+    while (ok && parts_done < xsg_result_num_parts(fin)) {
+      ok = harvest(fin, parts_done, prev);
+      ++parts_done;
+    }
+    xsg_result_timings(fin, &_timings);
+    xsg_result_free(fin);
+    if (prev.valid) release(prev);
+    if (carry_holder.valid) release(carry_holder);
+    if (!ok) throw std::runtime_error(detail::last_error("result copy"));
+    if constexpr (Tag::is_count) {
+      if (!_published) _result.add(std::vector<uint64_t>{0});  // empty input: the only running total is 0
+    }
+  }
+
+  const std::string _pattern;
+  Options _opt;
+  int _num_threads = 1, _num_readers = 1;
+  int _fd = -1;
+  uint64_t _size = 0;
+  bool _meta_mode = false;
+  std::vector<detail::Block> _blocks;
+  uint64_t _max_block = 0, _headroom = 0;
+
+  xsg_ctx* _ctx = nullptr;
+  xsg_stream* _stream = nullptr;
+  xsg_timings _timings{};
+
+  mutable std::mutex _m;  // guards _free, _ready, _next_block, _error
+  std::condition_variable _cv;
+  std::vector<std::unique_ptr<detail::Pinned>> _bufs;
+  std::vector<int> _free;
+  std::vector<int> _ready;
+  size_t _next_block = 0;
+  std::string _error;
+  std::atomic<bool> _failed{false};
+
+  std::mutex _join_m;
+  std::thread _pusher;
+  std::vector<std::thread> _readers;
+  std::atomic<bool> _running{false};
+
+  ResultT _result;
+  uint64_t _running_total = 0;
+  bool _published = false;
+};
+
+// ---- the one-call API -------------------------------------------------------------------------------------
+template <class Tag>
+std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path,
+                                             const std::string& meta_file_path, int num_threads = 1,
+                                             int max_num_readers = 1, Options opt = {}) {
+  return std::make_shared<Searcher<Tag>>(pattern, file_path, meta_file_path, num_threads, max_num_readers, opt);
+}
+
+// a string literal / char* meta path must not decay to the bool of the ignore_case overload
+template <class Tag>
+std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path,
+                                             const char* meta_file_path, int num_threads = 1, int max_num_readers = 1,
+                                             Options opt = {}) {
+  return std::make_shared<Searcher<Tag>>(pattern, file_path, std::string(meta_file_path ? meta_file_path : ""),
+                                         num_threads, max_num_readers, opt);
+}
+
+template <class Tag>
+std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path,
+                                             const std::string& meta_file_path, bool ignore_case, int num_threads,
+                                             int max_num_readers, Options opt = {}) {
+  if (ignore_case) throw std::invalid_argument("xs::extern_search: ignore_case is not part of the GPU literal path");
+  return std::make_shared<Searcher<Tag>>(pattern, file_path, meta_file_path, num_threads, max_num_readers, opt);
+}
+
+template <class Tag>
+std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path, bool ignore_case,
+                                             int num_threads = 1, Options opt = {}) {
+  if (ignore_case) throw std::invalid_argument("xs::extern_search: ignore_case is not part of the GPU literal path");
+  return std::make_shared<Searcher<Tag>>(pattern, file_path, std::string(), num_threads, 1, opt);
+}
+
+template <class Tag>
+std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path) {
+  return std::make_shared<Searcher<Tag>>(pattern, file_path, std::string(), 1, 1, Options{});
+}
+
+}  // namespace xs

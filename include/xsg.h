@@ -63,6 +63,7 @@ enum {
 typedef struct xsg_ctx xsg_ctx;       /* one device + stream + scratch */
 typedef struct xsg_corpus xsg_corpus; /* device-resident bytes + reference-chunk bounds */
 typedef struct xsg_result xsg_result; /* device-resident result vectors of one scan */
+typedef struct xsg_stream xsg_stream; /* a streamed search: segments are pushed, result parts appear */
 
 typedef struct xsg_scan_opts {
   uint64_t global_offset_base; /* added to every byte offset (shard / segment base)           */
@@ -135,11 +136,35 @@ int xsg_search_host(xsg_ctx* ctx, const void* host, uint64_t n, const uint64_t* 
                     uint64_t min_chunk, const uint8_t* pattern, uint32_t m, uint32_t kinds,
                     const xsg_scan_opts* opts, xsg_result** out);
 
+/* ---- streamed search (the reference's reader -> searcher -> result loop, Searcher.h:100-120,
+ *      tasks/readers.h:39-48, as a push interface) -------------------------------------------------
+ * A segment is a contiguous run of whole reference chunks: n host bytes (pinned memory for full
+ * speed) and the exclusive chunk ends RELATIVE to the segment start (bounds[nb-1] == n; every bound
+ * but the very last of the stream follows a '\n').  xsg_stream_push enqueues the H2D copy of the
+ * segment on the copy stream, then scans the PREVIOUS segment while that copy runs, and returns a
+ * ticket.  The host buffer may be reused once xsg_stream_wait_copied(ticket) has returned.  Results
+ * of finished segments are visible as parts of xsg_stream_result() (borrowed; parts only grow) --
+ * this is what the live iterator of the C++ layer reads.  xsg_stream_close scans the last segment,
+ * hands the complete result to the caller (who frees it) and destroys the stream. */
+int xsg_stream_open(xsg_ctx* ctx, const uint8_t* pattern, uint32_t m, uint32_t kinds, const xsg_scan_opts* opts,
+                    xsg_stream** out);
+int xsg_stream_push(xsg_stream* st, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb,
+                    uint64_t* ticket);
+int xsg_stream_wait_copied(xsg_stream* st, uint64_t ticket);
+const xsg_result* xsg_stream_result(const xsg_stream* st);
+int xsg_stream_close(xsg_stream* st, xsg_result** out);
+void xsg_stream_abort(xsg_stream* st); /* destroy without finishing */
+
 /* ---- results ---------------------------------------------------------------------------- */
 uint64_t xsg_result_count(const xsg_result* r, uint32_t kind);
 /* copy up to cap values of one vector kind to host memory (XSG_LINES: line starts) */
 int xsg_result_copy(const xsg_result* r, uint32_t kind, uint64_t* dst, uint64_t cap);
 int xsg_result_copy_line_lengths(const xsg_result* r, uint64_t* dst, uint64_t cap);
+/* part-wise access (one part per scanned segment, in file order) */
+uint64_t xsg_result_num_parts(const xsg_result* r);
+uint64_t xsg_result_part_count(const xsg_result* r, uint64_t part, uint32_t kind);
+int xsg_result_part_copy(const xsg_result* r, uint64_t part, uint32_t kind, uint64_t* dst, uint64_t cap);
+int xsg_result_part_copy_line_lengths(const xsg_result* r, uint64_t part, uint64_t* dst, uint64_t cap);
 /* device pointer of a result vector (stays valid until xsg_result_free) */
 const uint64_t* xsg_result_device_ptr(const xsg_result* r, uint32_t kind);
 uint64_t xsg_result_newlines(const xsg_result* r);        /* '\n' in the scanned bytes (line kinds) */

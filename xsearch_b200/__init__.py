@@ -45,7 +45,9 @@ EXPORTS = [
     "xsg_host_free", "xsg_corpus_alloc", "xsg_corpus_wrap", "xsg_corpus_free", "xsg_corpus_size",
     "xsg_corpus_device_ptr", "xsg_corpus_upload", "xsg_corpus_download", "xsg_corpus_fill_synth",
     "xsg_corpus_chunk", "xsg_corpus_set_bounds", "xsg_corpus_num_chunks", "xsg_corpus_get_bounds",
-    "xsg_synth_host", "xsg_chunk_bounds_host", "xsg_scan", "xsg_search_host", "xsg_result_count",
+    "xsg_synth_host", "xsg_chunk_bounds_host", "xsg_scan", "xsg_search_host", "xsg_stream_open", "xsg_stream_push",
+    "xsg_stream_wait_copied", "xsg_stream_result", "xsg_stream_close", "xsg_stream_abort", "xsg_result_num_parts",
+    "xsg_result_part_count", "xsg_result_part_copy", "xsg_result_part_copy_line_lengths", "xsg_result_count",
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
     "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_result_free",
 ]
@@ -114,6 +116,16 @@ def _load() -> C.CDLL:
         "xsg_scan": (i32, [vp, vp, C.c_char_p, u32, u32, C.POINTER(ScanOpts), C.POINTER(vp)]),
         "xsg_search_host": (i32, [vp, vp, u64, pu64, u64, u64, C.c_char_p, u32, u32, C.POINTER(ScanOpts),
                                   C.POINTER(vp)]),
+        "xsg_stream_open": (i32, [vp, C.c_char_p, u32, u32, C.POINTER(ScanOpts), C.POINTER(vp)]),
+        "xsg_stream_push": (i32, [vp, vp, u64, pu64, u64, pu64]),
+        "xsg_stream_wait_copied": (i32, [vp, u64]),
+        "xsg_stream_result": (vp, [vp]),
+        "xsg_stream_close": (i32, [vp, C.POINTER(vp)]),
+        "xsg_stream_abort": (None, [vp]),
+        "xsg_result_num_parts": (u64, [vp]),
+        "xsg_result_part_count": (u64, [vp, u64, u32]),
+        "xsg_result_part_copy": (i32, [vp, u64, u32, pu64, u64]),
+        "xsg_result_part_copy_line_lengths": (i32, [vp, u64, pu64, u64]),
         "xsg_result_count": (u64, [vp, u32]),
         "xsg_result_copy": (i32, [vp, u32, pu64, u64]),
         "xsg_result_copy_line_lengths": (i32, [vp, pu64, u64]),

@@ -1,0 +1,184 @@
+// xsgrep -- grep-like command line tool on top of xs::extern_search (the shape of the reference's
+// example/grep.cpp:66-80 and checkit.cpp).  Also the driver of the C++ API tests (tests/test_cpp_api.py).
+//
+//   xsgrep [--tag lines|count|count_lines|match_byte_offsets|line_byte_offsets|line_indices] [--meta FILE]
+//          [-j N] [--readers N] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D] [--live] PATTERN FILE
+//   xsgrep --selftest-host          host-only checks of the result collector (no GPU needed)
+//   xsgrep --metafile-cat FILE      print a v1 meta file (the reference's metafile_cat.cpp:23-49)
+#include <xsearch_b200/xsearch.hpp>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <string>
+
+namespace {
+
+struct Args {
+  std::string tag = "lines", meta, pattern, file;
+  int threads = 1, readers = 1;
+  bool live = false;
+  xs::Options opt;
+};
+
+template <class Tag>
+int run(const Args& a) {
+  auto searcher = xs::extern_search<Tag>(a.pattern, a.file, a.meta, a.threads, a.readers, a.opt);
+  auto* res = searcher->getResult();
+  if constexpr (Tag::is_count) {
+    uint64_t last = 0, yielded = 0;
+    if (a.live) {
+      for (auto v : *res) {  // running totals; the last one is the total
+        last = v;
+        ++yielded;
+      }
+      searcher->join();
+      if (last != res->size()) {
+        std::fprintf(stderr, "running total %llu != size %zu\n", (unsigned long long)last, res->size());
+        return 3;
+      }
+      std::fprintf(stderr, "yielded %llu running totals\n", (unsigned long long)yielded);
+    } else {
+      searcher->join();
+    }
+    std::cout << res->size() << '\n';
+  } else {
+    std::string out;
+    auto emit = [&out](const auto& v) {
+      if constexpr (std::is_same_v<typename Tag::value_type, std::string>) out += v;
+      else out += std::to_string(v);
+      out += '\n';
+      if (out.size() > (1u << 20)) {
+        std::fwrite(out.data(), 1, out.size(), stdout);
+        out.clear();
+      }
+    };
+    if (a.live) {
+      for (auto const& v : *res) emit(v);
+      searcher->join();
+    } else {
+      searcher->join();
+      for (auto const& v : res->copyResultSafe()) emit(v);
+    }
+    std::fwrite(out.data(), 1, out.size(), stdout);
+  }
+  if (!searcher->ok()) {
+    std::fprintf(stderr, "xsgrep: %s\n", searcher->error().c_str());
+    return 2;
+  }
+  const xsg_timings t = searcher->timings();
+  std::fprintf(stderr, "xsgrep: %llu bytes, pipeline %.1f ms (%.2f GB/s), device scans %.2f ms, %u kernel launches\n",
+               (unsigned long long)searcher->bytes(), t.h2d_ms, t.h2d_ms > 0 ? searcher->bytes() / t.h2d_ms / 1e6 : 0.0,
+               t.scan_ms, t.kernel_launches);
+  return 0;
+}
+
+int selftest_host() {
+  // blocking iterator: a producer thread adds parts with pauses, the consumer sees all of them in order
+  xs::Result<uint64_t> r(false);
+  std::thread prod([&] {
+    for (uint64_t p = 0; p < 5; ++p) {
+      std::this_thread::sleep_for(std::chrono::milliseconds(5));
+      r.add({p * 3, p * 3 + 1, p * 3 + 2});
+    }
+    r.close();
+  });
+  uint64_t expect = 0;
+  for (auto v : r) {
+    if (v != expect) return 1;
+    ++expect;
+  }
+  prod.join();
+  if (expect != 15 || r.size() != 15 || !r.is_closed() || r.add({1})) return 1;
+  if (r.copyResultSafe().size() != 15 || r.at(7) != 7) return 1;
+  // count tags: elements are running totals, size() is the total
+  xs::Result<uint64_t> c(true);
+  c.add({4});
+  c.add({9});
+  c.close();
+  uint64_t last = 0;
+  for (auto v : c) last = v;
+  if (last != 9 || c.size() != 9) return 1;
+  xs::Result<std::string> s(false);
+  s.close();
+  for (auto const& v : s) (void)v, std::abort();
+  // argument errors are exceptions, before any thread starts
+  try {
+    xs::extern_search<xs::count>("a\nb", "/nonexistent");
+    return 1;
+  } catch (const std::invalid_argument&) {
+  }
+  try {
+    xs::extern_search<xs::count>("abc", "/nonexistent/file");
+    return 1;
+  } catch (const std::runtime_error&) {
+  }
+  try {
+    xs::extern_search<xs::lines>("abc", "/etc/hostname", true, 1);
+    return 1;
+  } catch (const std::invalid_argument&) {
+  }
+  std::puts("selftest-host ok");
+  return 0;
+}
+
+int metafile_cat(const std::string& path) {
+  xs::MetaFile mf(path);
+  std::printf("compression_type: %u\nchunks: %zu\noriginal_size: %llu\n", (unsigned)mf.compression_type(),
+              mf.chunks().size(), (unsigned long long)mf.original_size());
+  for (const auto& c : mf.chunks())
+    std::printf("original_offset=%llu actual_offset=%llu original_size=%llu actual_size=%llu mappings=%zu first=(%llu,%llu)\n",
+                (unsigned long long)c.original_offset, (unsigned long long)c.actual_offset,
+                (unsigned long long)c.original_size, (unsigned long long)c.actual_size, c.line_mapping_data.size(),
+                (unsigned long long)(c.line_mapping_data.empty() ? 0 : c.line_mapping_data[0].globalByteOffset),
+                (unsigned long long)(c.line_mapping_data.empty() ? 0 : c.line_mapping_data[0].globalLineIndex));
+  return 0;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Args a;
+  std::vector<std::string> pos;
+  for (int i = 1; i < argc; ++i) {
+    const std::string s = argv[i];
+    auto next = [&]() -> std::string {
+      if (i + 1 >= argc) {
+        std::fprintf(stderr, "xsgrep: %s needs a value\n", s.c_str());
+        std::exit(64);
+      }
+      return argv[++i];
+    };
+    if (s == "--selftest-host") return selftest_host();
+    else if (s == "--metafile-cat") return metafile_cat(next());
+    else if (s == "--tag") a.tag = next();
+    else if (s == "--meta") a.meta = next();
+    else if (s == "-j") a.threads = std::atoi(next().c_str());
+    else if (s == "--readers") a.readers = std::atoi(next().c_str());
+    else if (s == "--min-chunk") a.opt.min_chunk = std::strtoull(next().c_str(), nullptr, 10);
+    else if (s == "--segment-bytes") a.opt.segment_bytes = std::strtoull(next().c_str(), nullptr, 10);
+    else if (s == "--device") a.opt.device = std::atoi(next().c_str());
+    else if (s == "--live") a.live = true;
+    else pos.push_back(s);
+  }
+  if (pos.size() != 2) {
+    std::fprintf(stderr, "usage: xsgrep [--tag T] [--meta FILE] [-j N] [--readers N] [--live] PATTERN FILE\n");
+    return 64;
+  }
+  a.pattern = pos[0];
+  a.file = pos[1];
+  try {
+    if (a.tag == "lines") return run<xs::lines>(a);
+    if (a.tag == "count" || a.tag == "count_matches") return run<xs::count>(a);
+    if (a.tag == "count_lines") return run<xs::count_lines>(a);
+    if (a.tag == "match_byte_offsets") return run<xs::match_byte_offsets>(a);
+    if (a.tag == "line_byte_offsets") return run<xs::line_byte_offsets>(a);
+    if (a.tag == "line_indices") return run<xs::line_indices>(a);
+    std::fprintf(stderr, "xsgrep: unknown tag %s\n", a.tag.c_str());
+    return 64;
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "xsgrep: %s\n", e.what());
+    return 1;
+  }
+}

@@ -53,6 +53,7 @@ struct xsg_ctx {
   xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2, selq, gran_mask;
   xsg::Scratch stage[2];               // streamed segments (double buffer)
   xsg::Scratch seg_bounds;
+  xsg::Scratch stage_bounds[2];        // chunk bounds of the streamed segments
   cudaEvent_t stage_copied[2] = {}, stage_free[2] = {};
   xsg::DevScalars* d_scalars = nullptr;
   xsg::DevScalars* h_scalars = nullptr;  // pinned
@@ -78,6 +79,14 @@ struct xsg_part {  // results of one device-resident scan (one streamed segment)
   uint64_t n_lines = 0;  // entries in line_start / line_len (xs::lines; may be n_line - 1)
 };
 
+namespace xsg {
+struct ScanStats {
+  uint64_t newlines = 0, raw = 0;
+  float main_ms = 0, post_ms = 0, scan_ms = 0;
+  uint32_t launches = 0;
+};
+}  // namespace xsg
+
 struct xsg_result {
   xsg_ctx* ctx = nullptr;
   uint32_t kinds = 0;
@@ -87,4 +96,20 @@ struct xsg_result {
   xsg_timings timings = {};
   // lazily concatenated device copies for xsg_result_device_ptr on multi-part results
   uint64_t* concat[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+struct xsg_stream {
+  xsg_ctx* ctx = nullptr;
+  xsg::Pattern pat;
+  uint32_t kinds = 0;
+  uint64_t goff_base = 0, lidx = 0, occ_cap = 0;
+  xsg_result* res = nullptr;
+  xsg::ScanStats st;
+  uint64_t pushed = 0;        // segments pushed so far (ticket of the next one)
+  uint64_t bytes_pushed = 0;  // global offset of the next segment
+  bool pending = false;       // segment pushed - 1 is copied (or being copied) but not scanned yet
+  uint64_t pend_n = 0, pend_off = 0, pend_nb = 0;
+  std::vector<uint64_t> h_bounds[2];
+  bool last_terminated = true;  // the previous segment ended with a newline
+  double t0 = 0;
 };

@@ -96,12 +96,6 @@ int alloc_out(xsg_ctx* ctx, uint64_t** p, uint64_t entries) {
   return XSG_OK;
 }
 
-struct ScanStats {
-  uint64_t newlines = 0, raw = 0;
-  float main_ms = 0, post_ms = 0, scan_ms = 0;
-  uint32_t launches = 0;
-};
-
 int read_scalars(xsg_ctx* ctx) {
   XSG_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(DevScalars), cudaMemcpyDeviceToHost, ctx->stream));
   XSG_CUDA(cudaStreamSynchronize(ctx->stream));
