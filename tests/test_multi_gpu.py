@@ -1,0 +1,119 @@
+"""Multi-GPU host logic: shard planning, the one exchange step and the ordered merge.
+
+CPU: two gloo ranks, each holding the per-shard results the GPU would produce (taken from the oracle run
+on the shard alone), must reassemble exactly the oracle's whole-file result.
+GPU (-m gpu): the same decomposition on one device, shard after shard, through xsg_scan + xsg_result_rebase."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import gen_cases
+import oracle_lib
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _corpus():
+    import xsearch_b200 as xs
+    p = xs.SynthParams.make(31, b"Sherlock", 30.0 / 4096)
+    buf = xs.synth_host(4096 * 700, p)
+    return buf, xs.chunk_bounds_host(buf, 200000)
+
+
+def test_shard_chunks_partition():
+    import xsearch_b200 as xs
+    buf, bounds = _corpus()
+    for world in (1, 2, 3, 4, 8, 64):
+        sh = xs.shard_chunks(bounds, world)
+        assert len(sh) == world and sh[0][0] == 0 and sh[-1][1] == bounds.size
+        assert all(a[1] == b[0] for a, b in zip(sh, sh[1:])) and all(c0 <= c1 for c0, c1 in sh)
+        if world <= 8:
+            sizes = [int(bounds[c1 - 1]) - (int(bounds[c0 - 1]) if c0 else 0) for c0, c1 in sh if c1 > c0]
+            assert max(sizes) - min(sizes) <= 2 * 260000  # balanced to about a chunk
+    assert xs.shard_chunks(np.zeros(0, np.uint64), 2) == [(0, 0), (0, 0)]
+
+
+def _rank_main(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch.distributed as dist
+    import xsearch_b200 as xs
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        oracle, _ = oracle_lib.load(build=False)
+        buf, bounds = _corpus()
+        c0, c1 = xs.shard_chunks(bounds, world)[rank]
+        b0 = int(bounds[c0 - 1]) if c0 else 0
+        b1 = int(bounds[c1 - 1]) if c1 > c0 else b0
+        shard, sb = buf[b0:b1], bounds[c0:c1] - np.uint64(b0)
+        pat = b"Sherlock"
+        # what this rank's GPU would hold after xsg_scan(offset_base = b0): shard-local results + byte base
+        match = oracle.match_byte_offsets(shard, pat, sb) + np.uint64(b0)
+        lidx = oracle.line_indices(shard, pat, sb)
+        newlines = int((shard == 10).sum())
+        line_base, bases, totals = xs.shard_exchange(newlines, [match.size, lidx.size])
+        lidx = lidx + np.uint64(line_base)  # == xsg_result_rebase(res, 0, line_base)
+        np.savez(os.path.join(out_dir, "rank%d.npz" % rank), match=match, lidx=lidx, bases=np.array(bases),
+                 totals=np.array(totals))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_two_rank_exchange_and_merge_gloo(tmp_path, world):
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_rank_main, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    exp_match = oracle.match_byte_offsets(buf, b"Sherlock", bounds)
+    exp_lidx = oracle.line_indices(buf, b"Sherlock", bounds)
+    parts = [np.load(os.path.join(str(tmp_path), "rank%d.npz" % r)) for r in range(world)]
+    assert np.array_equal(np.concatenate([p["match"] for p in parts]), exp_match)   # rank order == file order
+    assert np.array_equal(np.concatenate([p["lidx"] for p in parts]), exp_lidx)
+    off = 0
+    for p in parts:  # the output base of a rank is the number of results before it
+        assert int(p["bases"][0]) == off and int(p["totals"][0]) == exp_match.size and int(p["totals"][1]) == exp_lidx.size
+        off += p["match"].size
+
+
+@pytest.mark.gpu
+def test_shards_on_one_device_equal_whole():
+    import xsearch_b200 as xs
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    kinds = xs.MATCH_BYTE_OFFSETS | xs.LINE_BYTE_OFFSETS | xs.LINE_INDICES | xs.LINES | xs.COUNT | xs.COUNT_LINES
+    ctx = xs.Context(0)
+    for pat in (b"Sherlock", b"the"):
+        got = {k: [] for k in ("match", "loff", "lidx", "lst", "lln")}
+        line_base = cnt = cl = 0
+        for c0, c1 in xs.shard_chunks(bounds, 3):
+            b0 = int(bounds[c0 - 1]) if c0 else 0
+            corpus = ctx.corpus_from_host(buf[b0:int(bounds[c1 - 1])], bounds=bounds[c0:c1] - np.uint64(b0))
+            res = ctx.scan(corpus, pat, kinds, offset_base=b0)
+            res.rebase(0, line_base)             # the base the exchange would deliver
+            line_base += res.newlines
+            cnt += res.count(xs.COUNT)
+            cl += res.count(xs.COUNT_LINES)
+            got["match"].append(res.vector(xs.MATCH_BYTE_OFFSETS))
+            got["loff"].append(res.vector(xs.LINE_BYTE_OFFSETS))
+            got["lidx"].append(res.vector(xs.LINE_INDICES))
+            st, ln = res.line_spans()
+            got["lst"].append(st)
+            got["lln"].append(ln)
+            res.free()
+            corpus.free()
+        assert cnt == oracle.count(buf, pat, bounds, False) and cl == oracle.count(buf, pat, bounds, True)
+        assert np.array_equal(np.concatenate(got["match"]), oracle.match_byte_offsets(buf, pat, bounds))
+        assert np.array_equal(np.concatenate(got["loff"]), oracle.line_byte_offsets(buf, pat, bounds))
+        assert np.array_equal(np.concatenate(got["lidx"]), oracle.line_indices(buf, pat, bounds))
+        est, eln = oracle.lines(buf, pat, bounds)
+        assert np.array_equal(np.concatenate(got["lst"]), est) and np.array_equal(np.concatenate(got["lln"]), eln)
+    ctx.close()

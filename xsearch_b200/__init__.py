@@ -152,7 +152,7 @@ def _check(rc: int) -> None:
 
 
 from .api import (Context, Corpus, Result, Searcher, extern_search, synth_host, chunk_bounds_host,  # noqa: E402
-                  shard_exchange)
+                  shard_chunks, shard_exchange, sharded_scan)
 
 __all__ = ["Context", "Corpus", "Result", "Searcher", "extern_search", "synth_host", "chunk_bounds_host",
-           "shard_exchange", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]
+           "shard_chunks", "shard_exchange", "sharded_scan", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]

@@ -306,6 +306,28 @@ def extern_search(tag, pattern, file_path: str, meta_file: Optional[str] = None,
     return Searcher(kind, pattern, file_path, meta_file, num_threads, max_num_readers, **kw)
 
 
+def shard_chunks(bounds: np.ndarray, world: int) -> List[Tuple[int, int]]:
+    """Contiguous, newline-aligned shards for `world` ranks: reference chunks [c0, c1) per rank, balanced by
+    bytes.  Shard boundaries are chunk boundaries, so no line, no match and no tail zone spans two GPUs
+    (SURVEY.md 8(e)); ranks beyond the number of chunks get an empty range."""
+    nb = int(bounds.size)
+    total = int(bounds[-1]) if nb else 0
+    out, c0 = [], 0
+    for r in range(world):
+        if r == world - 1:
+            c1 = nb
+        else:
+            target = total * (r + 1) // world
+            c1 = int(np.searchsorted(bounds, target, side="left")) + 1 if target > 0 else c0
+            c1 = max(c0, min(c1, nb))
+            # take the chunk whose end is nearest to the ideal cut
+            if c1 - 1 > c0 and abs(int(bounds[c1 - 2]) - target) <= abs(int(bounds[c1 - 1]) - target):
+                c1 -= 1
+        out.append((c0, c1))
+        c0 = c1
+    return out
+
+
 def shard_exchange(newlines: int, counts: Sequence[int], group=None) -> Tuple[int, List[int], List[int]]:
     """The one exchange step of the multi-GPU path: all-gather every shard's {newline count, result
     counts}; returns (line-index base of this rank, output bases per count, global totals)."""
@@ -325,3 +347,15 @@ def shard_exchange(newlines: int, counts: Sequence[int], group=None) -> Tuple[in
     excl = table[:rank].sum(axis=0) if rank else np.zeros(table.shape[1], dtype=np.int64)
     tot = table.sum(axis=0)
     return int(excl[0]), [int(x) for x in excl[1:]], [int(x) for x in tot[1:]]
+
+
+def sharded_scan(ctx: "Context", corpus: "Corpus", pattern: bytes, kinds: int, shard_base: int, group=None):
+    """One rank's part of a multi-GPU search: scan the local shard with its global byte base, exchange
+    {newlines, counts} with the other ranks, add the global line-number base on the device.
+    Returns (result, output bases per requested kind, global totals per requested kind)."""
+    res = ctx.scan(corpus, pattern, kinds, offset_base=shard_base)
+    ks = [k for k in (COUNT, COUNT_LINES, MATCH_BYTE_OFFSETS, LINE_BYTE_OFFSETS, LINE_INDICES, LINES) if kinds & k]
+    line_base, bases, totals = shard_exchange(res.newlines, [res.count(k) for k in ks], group)
+    if line_base:
+        res.rebase(0, line_base)
+    return res, dict(zip(ks, bases)), dict(zip(ks, totals))
