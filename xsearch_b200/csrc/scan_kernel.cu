@@ -201,45 +201,62 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
 // ---- pass 2: ordered emission from the stored masks.  The output position of a granule is the
 // exclusive prefix of the granule counts, so there is no inter-CTA dependency.  A warp inspects 32
 // granule counters at a time and expands the masks of the non-empty ones (512 bytes each).
+//
+// Pass 1 stores a mask as [lane][row] halfwords (one 16-byte store per lane).  Here lane L gathers the
+// eight halfwords of row L/4, lanes 8(L%4)..8(L%4)+7: 128 mask bits that cover the CONTIGUOUS byte range
+// [128 L, 128 L + 128) of the granule.  File order is then lane order, one warp scan of the per-lane
+// popcounts yields every slot, and each lane writes its own hits.
+struct GranMask {
+  uint32_t w[4];
+  unsigned long long base;
+};
+
+__device__ __forceinline__ void load_gran_mask(const ScanArgs& a, uint64_t g, int lane, GranMask& m) {
+  const uint16_t* __restrict__ h =
+      reinterpret_cast<const uint16_t*>(a.gran_mask + g * 32) + (8 * (lane & 3)) * 8 + (lane >> 2);
+  uint32_t t[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) t[j] = __ldg(h + j * 8);  // lane 8(L%4)+j, row L/4
+#pragma unroll
+  for (int k = 0; k < 4; ++k) m.w[k] = t[2 * k] | (t[2 * k + 1] << 16);
+  m.base = a.gran_prefix[g];
+}
+
 __global__ void __launch_bounds__(kThreads)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
   const uint64_t n_gran = a.n_tiles * kWarps;
-  {  // one warp per unit of 32 granules: the serial part of a warp is the handful of hit granules of its unit
-    const uint64_t g0 = ((uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5)) * 32;
-    if (g0 >= n_gran) return;
-    const uint64_t gi = g0 + lane;
-    const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
-    unsigned todo = __ballot_sync(kFull, c != 0);
-    while (todo) {
-      const int src = __ffs(todo) - 1;
-      todo &= todo - 1;
-      const uint64_t g = g0 + src;
-      const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
-      const uint4 mk = a.gran_mask[g * 32 + lane];
-      const uint32_t mask[kRows / 2] = {mk.x, mk.y, mk.z, mk.w};
-      unsigned long long base = a.gran_prefix[g];
-      const uint64_t lane_off = gran_off + (uint64_t)lane * 16 - pat.anchor;
+  // one warp per unit of 32 granules: the serial part of a warp is the handful of hit granules of its unit
+  const uint64_t g0 = ((uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5)) * 32;
+  if (g0 >= n_gran) return;
+  const uint64_t gi = g0 + lane;
+  const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
+  unsigned todo = __ballot_sync(kFull, c != 0);
+  // software pipeline: the mask and prefix of the next hit granule are in flight while this one is expanded
+  GranMask next{};
+  if (todo) load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const GranMask cur = next;
+    if (todo) load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
+    const uint32_t cnt = __popc(cur.w[0]) + __popc(cur.w[1]) + __popc(cur.w[2]) + __popc(cur.w[3]);
+    uint32_t inc = cnt;  // inclusive warp scan of the per-lane counts
 #pragma unroll
-      for (int u = 0; u < kRows; ++u) {
-        uint32_t m16 = (mask[u >> 1] >> (16 * (u & 1))) & 0xffffu;
-        const uint32_t cu = __popc(m16);
-        if (!__any_sync(kFull, cu != 0)) continue;
-        uint32_t inc = cu;  // inclusive warp scan of the per-lane counts of this row
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(kFull, inc, o);
+      if (lane >= o) inc += t;
+    }
+    unsigned long long slot = cur.base + (inc - cnt);
+    const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes + (uint64_t)lane * 128 - pat.anchor + a.occ_add;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t t = __shfl_up_sync(kFull, inc, o);
-          if (lane >= o) inc += t;
-        }
-        unsigned long long slot = base + (inc - cu);
-        base += __shfl_sync(kFull, inc, 31);
-        const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
-        while (m16) {
-          const int b = __ffs(m16) - 1;
-          m16 &= m16 - 1;
-          if (slot < a.occ_cap) a.occ[slot] = pos0 + b;
-          ++slot;
-        }
+    for (int k = 0; k < 4; ++k) {
+      uint32_t w = cur.w[k];
+      while (w) {
+        const int b = __ffs(w) - 1;
+        w &= w - 1;
+        if (slot < a.occ_cap) a.occ[slot] = pos0 + 32 * k + b;
+        ++slot;
       }
     }
   }

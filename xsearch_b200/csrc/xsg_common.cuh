@@ -39,6 +39,7 @@ struct ScanArgs {
   const uint64_t* gran_prefix;  // [granules] exclusive prefix of gran_count (pass 2)
   uint64_t* occ;             // raw occurrence list (pass 2)
   uint64_t occ_cap;
+  uint64_t occ_add;          // added to every emitted position (direct mode: the global offset base)
 };
 
 // launchers implemented in scan_kernel.cu
@@ -56,6 +57,8 @@ struct ListArgs {
   uint8_t* sel;            // [k] selection flags (output of select / zone kernels)
   const uint64_t* gran_prefix;  // [n_gran + 1] exclusive prefix of the granule counts (brackets searches in occ) or nullptr
   uint64_t n_gran;
+  uint64_t bias;                // the list holds position + bias (direct mode: the global offset base)
+  unsigned long long* drops;    // direct mode (sel == nullptr): occurrences the reference's chunk tails do not report
 };
 
 // small helpers usable from host code

@@ -35,6 +35,7 @@ struct DevScalars {
   unsigned long long zone_sub, zone_add;
   unsigned long long sel_total[2];  // [0] match family, [1] line family
   unsigned long long nb_out;
+  unsigned long long drops;
   unsigned int unterminated;
   unsigned int bad_bounds;
   unsigned int ticket[4];

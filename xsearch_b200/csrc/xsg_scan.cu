@@ -164,38 +164,66 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
                        ctx->scan_tmp.as<uint64_t>(), s);
     XSG_CUDA(cudaGetLastError());
     st->launches += 4;
-    // pass 2: positions of the occurrences (re-reads only granules that hold any)
-    uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
-    if (ctx->occ.cap / sizeof(uint64_t) > cap && !occ_cap_opt) cap = ctx->occ.cap / sizeof(uint64_t);
-    // the host needs the number of occurrences (allocation sizes, grids); it travels while pass 2 runs
+    // pass 2: positions of the occurrences, expanded from the masks of the granules that hold any.
+    // The host needs their number (allocation sizes, grids).
     XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
                              cudaMemcpyDeviceToHost, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[4], s));
-    if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
-    a.occ = ctx->occ.as<uint64_t>();
-    a.occ_cap = cap;
-    XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
-    st->launches += 1;
-    XSG_CUDA(cudaEventSynchronize(ctx->ev[4]));
-    const uint64_t k = ctx->h_scalars->occ_total;
-    if (k > cap) {  // rare: denser than the estimate -> emit again with the exact capacity
-      XSG_CUDA(cudaStreamSynchronize(s));
-      if ((rc = ctx->occ.reserve(k * sizeof(uint64_t)))) return rc;
-      a.occ = ctx->occ.as<uint64_t>();
+    // direct mode: for xs::match_byte_offsets of a pattern that cannot overlap itself the occurrence list
+    // IS the result unless a chunk tail of the reference drops one (rare) -- so pass 2 writes global
+    // offsets straight into the result vector and the list kernels read it with a bias
+    const bool direct = (kinds & XSG_MATCH_BYTE_OFFSETS) && !pat.bordered;
+    uint64_t k = 0;
+    uint64_t* occ_list = nullptr;
+    if (direct) {
+      XSG_CUDA(cudaEventSynchronize(ctx->ev[4]));
+      k = ctx->h_scalars->occ_total;
+      if ((rc = alloc_out(ctx, &part->match_off, k))) return rc;
+      occ_list = part->match_off;
+      a.occ = occ_list;
       a.occ_cap = k;
-      XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+      a.occ_add = goff;
+      if (k) {
+        XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+        st->launches += 1;
+      }
+    } else {
+      uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
+      if (ctx->occ.cap / sizeof(uint64_t) > cap && !occ_cap_opt) cap = ctx->occ.cap / sizeof(uint64_t);
+      if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
+      a.occ = ctx->occ.as<uint64_t>();
+      a.occ_cap = cap;
+      XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));  // the count travels to the host while this runs
       st->launches += 1;
+      XSG_CUDA(cudaEventSynchronize(ctx->ev[4]));
+      k = ctx->h_scalars->occ_total;
+      if (k > cap) {  // rare: denser than the estimate -> emit again with the exact capacity
+        XSG_CUDA(cudaStreamSynchronize(s));
+        if ((rc = ctx->occ.reserve(k * sizeof(uint64_t)))) return rc;
+        a.occ = ctx->occ.as<uint64_t>();
+        a.occ_cap = k;
+        XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+        st->launches += 1;
+      }
+      occ_list = ctx->occ.as<uint64_t>();
     }
     st->raw += k;
     if (k > 0) {
       if ((rc = ctx->sel.reserve(k))) return rc;
       const uint64_t n_ct = div_up(k, 2048);
       if ((rc = ctx->desc2.reserve(n_ct * sizeof(unsigned long long)))) return rc;
-      ListArgs l{buf, n, d_bounds, nb, ctx->occ.as<uint64_t>(), k, ctx->sel.as<uint8_t>(),
-                 ctx->gran_prefix.as<uint64_t>(), n_gran};
+      ListArgs l{buf, n, d_bounds, nb, occ_list, k, ctx->sel.as<uint8_t>(), ctx->gran_prefix.as<uint64_t>(), n_gran,
+                 direct ? goff : 0, &ds->drops};
       for (int fam = 0; fam < 2; ++fam) {
         if (fam == 0 ? !want_match : !want_line) continue;
         const int mode = fam == 1 ? kSelLine : (pat.bordered ? kSelMatchBordered : kSelMatch);
+        if (fam == 0 && direct) {  // only count what the reference's chunk tails would not report
+          ListArgs ld = l;
+          ld.sel = nullptr;
+          launch_zone(ld, pat, mode, s);
+          st->launches += pat.m > 1 ? 1 : 0;
+          continue;
+        }
         launch_select(l, pat, mode, s);
         launch_zone(l, pat, mode, s);
         st->launches += 1 + (pat.m > 1 ? 1 : 0);
@@ -241,6 +269,34 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     }
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
+    if (direct && k > 0 && ctx->h_scalars->drops) {
+      // a chunk tail of the reference skipped occurrences: select + compact the list into a new vector
+      ListArgs l{buf, n, d_bounds, nb, occ_list, k, ctx->sel.as<uint8_t>(), ctx->gran_prefix.as<uint64_t>(), n_gran,
+                 goff, &ds->drops};
+      launch_select(l, pat, kSelMatch, s);
+      launch_zone(l, pat, kSelMatch, s);
+      CompactArgs c{};
+      c.l = l;
+      c.goff = goff;
+      uint64_t* fixed = nullptr;
+      if ((rc = alloc_out(ctx, &fixed, k))) return rc;
+      c.out_match = fixed;
+      const uint64_t n_ct = div_up(k, 2048);
+      c.desc = ctx->desc2.as<unsigned long long>();
+      c.ticket = &ds->ticket[1];
+      c.total = &ds->sel_total[0];
+      c.unterminated = &ds->unterminated;
+      XSG_CUDA(cudaMemsetAsync(c.desc, 0, n_ct * sizeof(unsigned long long), s));
+      launch_compact(c, pat, s);
+      XSG_CUDA(cudaGetLastError());
+      st->launches += 3;
+      XSG_CUDA(cudaFreeAsync(part->match_off, s));
+      part->match_off = fixed;
+      XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
+      if ((rc = read_scalars(ctx))) return rc;
+    } else if (direct) {
+      ctx->h_scalars->sel_total[0] = k;
+    }
     const DevScalars& h = *ctx->h_scalars;
     part->n_match = h.sel_total[0];
     part->n_line = h.sel_total[1];
