@@ -174,6 +174,13 @@ int xsg_result_timings(const xsg_result* r, xsg_timings* t);
  * every line index of a finished result, on the device -- the global line-number base of a shard
  * is only known after the exchange of all shards' newline counts. */
 int xsg_result_rebase(xsg_result* r, uint64_t offset_delta, uint64_t line_index_delta);
+/* The same fix-up without a host round trip.  xsg_scan_summary_device() points at 4 u64 in device
+ * memory, {newlines, matches, matching lines, lines} of the LAST scan of this context (written in stream
+ * order at the end of xsg_scan; valid until the next scan).  After an all-gather of every rank's summary
+ * into table[world][stride] (NCCL, on the context's stream), xsg_result_rebase_from_table adds
+ * sum(table[r][0] for r < rank) to every line index, reading the table on the device. */
+const uint64_t* xsg_scan_summary_device(xsg_ctx* ctx);
+int xsg_result_rebase_from_table(xsg_result* r, const uint64_t* table_dev, uint32_t stride, uint32_t rank);
 void xsg_result_free(xsg_result* r);
 
 #ifdef __cplusplus

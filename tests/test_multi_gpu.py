@@ -117,3 +117,34 @@ def test_shards_on_one_device_equal_whole():
         est, eln = oracle.lines(buf, pat, bounds)
         assert np.array_equal(np.concatenate(got["lst"]), est) and np.array_equal(np.concatenate(got["lln"]), eln)
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_device_side_summary_and_table_rebase():
+    """The host-free exchange: the scan's summary lives on the device, the fix-up kernel reads the gathered table."""
+    import torch
+    import xsearch_b200 as xs
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    ctx = xs.Context(0)
+    corpus = ctx.corpus_from_host(buf, bounds=bounds)
+    kinds = xs.COUNT | xs.COUNT_LINES | xs.LINE_INDICES | xs.LINES | xs.MATCH_BYTE_OFFSETS
+    res = ctx.scan(corpus, b"Sherlock", kinds)
+    torch.cuda.synchronize()
+    summ = ctx.summary_tensor().cpu().numpy()
+    assert list(summ) == [res.newlines, res.count(xs.COUNT), res.count(xs.COUNT_LINES), res.count(xs.LINES)]
+    assert summ[0] == int((buf == 10).sum())
+    # pretend to be rank 2 of 3: ranks 0 and 1 hold 1000 and 234 newlines
+    table = torch.tensor([[1000, 1, 1, 1], [234, 2, 2, 2], [int(summ[0]), 3, 3, 3]], dtype=torch.int64, device="cuda")
+    res.rebase_from_table(table, 2)
+    torch.cuda.synchronize()
+    assert np.array_equal(res.vector(xs.LINE_INDICES), oracle.line_indices(buf, b"Sherlock", bounds) + np.uint64(1234))
+    assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), oracle.match_byte_offsets(buf, b"Sherlock", bounds))
+    res.free()
+    # count-only and direct paths fill the summary as well
+    res = ctx.scan(corpus, b"Sherlock", xs.COUNT)
+    torch.cuda.synchronize()
+    assert int(ctx.summary_tensor()[1].item()) == res.count(xs.COUNT) == oracle.count(buf, b"Sherlock", bounds, False)
+    res.free()
+    corpus.free()
+    ctx.close()

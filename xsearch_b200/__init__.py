@@ -49,7 +49,7 @@ EXPORTS = [
     "xsg_stream_wait_copied", "xsg_stream_result", "xsg_stream_close", "xsg_stream_abort", "xsg_result_num_parts",
     "xsg_result_part_count", "xsg_result_part_copy", "xsg_result_part_copy_line_lengths", "xsg_result_count",
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
-    "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_result_free",
+    "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_scan_summary_device", "xsg_result_rebase_from_table", "xsg_result_free",
 ]
 
 
@@ -134,6 +134,8 @@ def _load() -> C.CDLL:
         "xsg_result_raw_occurrences": (u64, [vp]),
         "xsg_result_timings": (i32, [vp, C.POINTER(Timings)]),
         "xsg_result_rebase": (i32, [vp, u64, u64]),
+        "xsg_scan_summary_device": (vp, [vp]),
+        "xsg_result_rebase_from_table": (i32, [vp, vp, u32, u32]),
         "xsg_result_free": (None, [vp]),
     }
     for name, (res, args) in sig.items():
@@ -152,7 +154,7 @@ def _check(rc: int) -> None:
 
 
 from .api import (Context, Corpus, Result, Searcher, extern_search, synth_host, chunk_bounds_host,  # noqa: E402
-                  shard_chunks, shard_exchange, sharded_scan)
+                  shard_chunks, shard_exchange, sharded_scan, sharded_scan_async)
 
 __all__ = ["Context", "Corpus", "Result", "Searcher", "extern_search", "synth_host", "chunk_bounds_host",
-           "shard_chunks", "shard_exchange", "sharded_scan", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]
+           "shard_chunks", "shard_exchange", "sharded_scan", "sharded_scan_async", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]

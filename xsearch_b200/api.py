@@ -75,6 +75,19 @@ class Context:
         """Run the context's device work on a caller-owned CUDA stream (0/None = its own stream)."""
         _check(lib.xsg_set_stream(self._h, C.c_void_p(cuda_stream or None)))
 
+    def summary_tensor(self):
+        """Zero-copy torch view (int64[4], on this device) of {newlines, matches, matching lines, lines} of the
+        context's last scan -- the input of the multi-GPU all-gather (xsg_scan_summary_device)."""
+        import torch
+        if getattr(self, "_summary", None) is None:
+            ptr = lib.xsg_scan_summary_device(self._h)
+
+            class _View:
+                __cuda_array_interface__ = {"shape": (4,), "typestr": "<i8", "data": (int(ptr), False), "version": 2}
+
+            self._summary = torch.as_tensor(_View(), device=torch.device("cuda", self.device))
+        return self._summary
+
     # -- corpora ----------------------------------------------------------------------------
     def corpus(self, n_bytes: int) -> "Corpus":
         h = C.c_void_p()
@@ -218,6 +231,11 @@ class Result:
         """Multi-GPU fix-up: add the shard's global byte / line-number base on the device."""
         _check(lib.xsg_result_rebase(self._h, offset_delta, line_index_delta))
 
+    def rebase_from_table(self, table, rank: int) -> None:
+        """Device-side fix-up after an all-gather of every rank's summary into `table` (torch int64
+        [world, stride] on this device): adds sum(table[r][0] for r < rank) to every line index."""
+        _check(lib.xsg_result_rebase_from_table(self._h, C.c_void_p(table.data_ptr()), int(table.stride(0)), rank))
+
     def timings(self) -> Timings:
         t = Timings()
         _check(lib.xsg_result_timings(self._h, C.byref(t)))
@@ -347,6 +365,19 @@ def shard_exchange(newlines: int, counts: Sequence[int], group=None) -> Tuple[in
     excl = table[:rank].sum(axis=0) if rank else np.zeros(table.shape[1], dtype=np.int64)
     tot = table.sum(axis=0)
     return int(excl[0]), [int(x) for x in excl[1:]], [int(x) for x in tot[1:]]
+
+
+def sharded_scan_async(ctx: "Context", corpus: "Corpus", pattern: bytes, kinds: int, shard_base: int, table,
+                       group=None) -> "Result":
+    """Like sharded_scan, but the exchange never returns to the host: the scan's device-resident summary is
+    all-gathered into `table` (int64 [world, 4] on this device, caller-owned) on the current torch stream --
+    which must be the stream the context runs on (Context.set_stream) -- and the line-index base is added
+    by a kernel that reads the table.  Global totals are table[:, 1:].sum(0) whenever the caller wants them."""
+    import torch.distributed as dist
+    res = ctx.scan(corpus, pattern, kinds, offset_base=shard_base)
+    dist.all_gather_into_tensor(table.view(-1), ctx.summary_tensor(), group=group)
+    res.rebase_from_table(table, dist.get_rank(group))
+    return res
 
 
 def sharded_scan(ctx: "Context", corpus: "Corpus", pattern: bytes, kinds: int, shard_base: int, group=None):

@@ -237,7 +237,33 @@ __global__ void add_u64_kernel(uint64_t* v, uint64_t n, uint64_t delta) {
     v[i] += delta;
 }
 
+__global__ void add_u64_from_table_kernel(uint64_t* v, uint64_t n, const uint64_t* __restrict__ table, uint32_t stride,
+                                          uint32_t rank) {
+  uint64_t delta = 0;
+  for (uint32_t r = 0; r < rank; ++r) delta += table[(uint64_t)r * stride];
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    v[i] += delta;
+}
+
+__global__ void summary_kernel(const DevScalars* __restrict__ d, int mode, int want_lines, unsigned long long* out) {
+  out[0] = d->nl_total;
+  out[1] = mode == 1 ? d->occ_total - d->zone_sub + d->zone_add : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
+  out[2] = d->sel_total[1];
+  out[3] = want_lines ? d->sel_total[1] - (d->unterminated ? 1 : 0) : 0;
+}
+
 }  // namespace
+
+void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, cudaStream_t s) {
+  summary_kernel<<<1, 1, 0, s>>>(static_cast<const DevScalars*>(dev_scalars), mode, want_lines, summary);
+}
+
+void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, uint32_t stride, uint32_t rank,
+                               cudaStream_t s) {
+  if (n == 0 || rank == 0) return;
+  const uint64_t want = div_up(n, 256);
+  add_u64_from_table_kernel<<<(unsigned)(want < 4736 ? want : 4736), 256, 0, s>>>(v, n, table, stride, rank);
+}
 
 void launch_add_u64(uint64_t* v, uint64_t n, uint64_t delta, cudaStream_t s) {
   if (n == 0 || delta == 0) return;

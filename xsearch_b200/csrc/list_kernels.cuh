@@ -57,5 +57,11 @@ void launch_compact(const CompactArgs& a, const Pattern& pat, cudaStream_t s);
 
 // v[i] += delta (multi-GPU rebase of offsets / line indices)
 void launch_add_u64(uint64_t* v, uint64_t n, uint64_t delta, cudaStream_t s);
+// v[i] += sum(table[r * stride] for r < rank), the table read on the device
+void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, uint32_t stride, uint32_t rank,
+                               cudaStream_t s);
+// summary[0..4) = {newlines, matches, matching lines, lines} from the scan's device scalars
+// mode 0: list path, 1: count-only path (occ_total - zone_sub + zone_add), 2: direct path (occ_total - drops)
+void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, cudaStream_t s);
 
 }  // namespace xsg

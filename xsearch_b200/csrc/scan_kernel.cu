@@ -247,16 +247,20 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
       const uint32_t t = __shfl_up_sync(kFull, inc, o);
       if (lane >= o) inc += t;
     }
-    unsigned long long slot = cur.base + (inc - cnt);
-    const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes + (uint64_t)lane * 128 - pat.anchor + a.occ_add;
+    const unsigned long long slot = cur.base + (inc - cnt);
+    // one capacity check per lane instead of one per store (the list is sized from the exact total;
+    // it only overflows on the estimate-based first attempt of the non-direct path)
+    if (slot + cnt <= a.occ_cap) {
+      uint64_t* __restrict__ out = a.occ + slot;
+      const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes + (uint64_t)lane * 128 - pat.anchor + a.occ_add;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      uint32_t w = cur.w[k];
-      while (w) {
-        const int b = __ffs(w) - 1;
-        w &= w - 1;
-        if (slot < a.occ_cap) a.occ[slot] = pos0 + 32 * k + b;
-        ++slot;
+      for (int k = 0; k < 4; ++k) {
+        uint32_t w = cur.w[k];
+        while (w) {
+          const int b = __ffs(w) - 1;
+          w &= w - 1;
+          *out++ = pos0 + (uint32_t)(32 * k + b);
+        }
       }
     }
   }

@@ -84,6 +84,8 @@ int xsg_init(int device, xsg_ctx** out) {
     XSG_CUDA(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
   }
   XSG_CUDA(cudaMalloc(&c->d_scalars, sizeof(DevScalars)));
+  XSG_CUDA(cudaMalloc(&c->d_summary, 4 * sizeof(unsigned long long)));
+  XSG_CUDA(cudaMemset(c->d_summary, 0, 4 * sizeof(unsigned long long)));
   XSG_CUDA(cudaHostAlloc(&c->h_scalars, sizeof(DevScalars), cudaHostAllocDefault));
   // keep freed result memory in the stream-ordered pool instead of returning it to the driver
   cudaMemPool_t pool;
@@ -110,6 +112,7 @@ void xsg_destroy(xsg_ctx* c) {
     cudaEventDestroy(c->stage_free[i]);
   }
   cudaFree(c->d_scalars);
+  cudaFree(c->d_summary);
   cudaFreeHost(c->h_scalars);
   cudaStreamDestroy(c->own_stream);
   cudaStreamDestroy(c->copy_stream);

@@ -61,7 +61,21 @@ struct ListArgs {
   unsigned long long* drops;    // direct mode (sel == nullptr): occurrences the reference's chunk tails do not report
 };
 
+// device scalars of one scan (zeroed at the start, read back through a pinned mirror)
+struct DevScalars {
+  unsigned long long nl_total;
+  unsigned long long occ_total;
+  unsigned long long zone_sub, zone_add;
+  unsigned long long sel_total[2];  // [0] match family, [1] line family
+  unsigned long long nb_out;
+  unsigned long long drops;
+  unsigned int unterminated;
+  unsigned int bad_bounds;
+  unsigned int ticket[4];
+  unsigned int pad[2];
+};
 // small helpers usable from host code
+
 inline uint64_t div_up(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
 
 // ---- device helpers -------------------------------------------------------------------------

@@ -28,20 +28,6 @@ struct Scratch {
   template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
-// device scalars of one scan (zeroed at the start, read back through a pinned mirror)
-struct DevScalars {
-  unsigned long long nl_total;
-  unsigned long long occ_total;
-  unsigned long long zone_sub, zone_add;
-  unsigned long long sel_total[2];  // [0] match family, [1] line family
-  unsigned long long nb_out;
-  unsigned long long drops;
-  unsigned int unterminated;
-  unsigned int bad_bounds;
-  unsigned int ticket[4];
-  unsigned int pad[2];
-};
-
 }  // namespace xsg
 
 struct xsg_ctx {
@@ -57,6 +43,7 @@ struct xsg_ctx {
   xsg::Scratch stage_bounds[2];        // chunk bounds of the streamed segments
   cudaEvent_t stage_copied[2] = {}, stage_free[2] = {};
   xsg::DevScalars* d_scalars = nullptr;
+  unsigned long long* d_summary = nullptr;  // {newlines, matches, matching lines, lines} of the last scan
   xsg::DevScalars* h_scalars = nullptr;  // pinned
 };
 

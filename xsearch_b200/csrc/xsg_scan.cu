@@ -111,6 +111,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   XSG_CUDA(cudaEventRecord(ctx->ev[0], s));
   XSG_CUDA(cudaMemsetAsync(ctx->d_scalars, 0, sizeof(DevScalars), s));
   if (n == 0 || nb == 0) {
+    XSG_CUDA(cudaMemsetAsync(ctx->d_summary, 0, 4 * sizeof(unsigned long long), s));
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     XSG_CUDA(cudaStreamSynchronize(s));
     return XSG_OK;
@@ -137,7 +138,8 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     launch_reduce_u32(a.gran_count, n_gran, &ds->occ_total, s);
     launch_zone_count(buf, n, d_bounds, nb, pat, a.gran_count, &ds->zone_sub, &ds->zone_add, s);
     XSG_CUDA(cudaGetLastError());
-    st->launches += 2 + (pat.m > 1 ? 1 : 0);
+    launch_summary(ds, 1, 0, ctx->d_summary, s);
+    st->launches += 3 + (pat.m > 1 ? 1 : 0);
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
     const DevScalars& h = *ctx->h_scalars;
@@ -267,6 +269,8 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         st->launches += c.selq ? 2 : 1;
       }
     }
+    launch_summary(ds, direct ? 2 : 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, s);
+    st->launches += 1;
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
     if (direct && k > 0 && ctx->h_scalars->drops) {
@@ -289,7 +293,8 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       XSG_CUDA(cudaMemsetAsync(c.desc, 0, n_ct * sizeof(unsigned long long), s));
       launch_compact(c, pat, s);
       XSG_CUDA(cudaGetLastError());
-      st->launches += 3;
+      launch_summary(ds, 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, s);
+      st->launches += 4;
       XSG_CUDA(cudaFreeAsync(part->match_off, s));
       part->match_off = fixed;
       XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
