@@ -43,8 +43,8 @@ __device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t
 // operations: bit 7 of ((w ^ c) & 0x7f) + 0x7f is set iff the low seven bits differ from c; bit 7 of
 // w itself differs from c iff it is set (c = 0x0a has it clear), so the xor is not needed for the
 // final OR.  The four 0x80 flags are summed by one dp4a instead of popc + add.
-__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc) {
-  const uint32_t b = ((w ^ 0x0a0a0a0au) & k7F) + k7F;
+__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc, uint32_t c_nl, uint32_t c_7f) {
+  const uint32_t b = ((w ^ c_nl) & c_7f) + k7F;
   return __dp4a((b | w) & k80, k01, acc);
 }
 
@@ -111,10 +111,10 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
     if (NL) {  // 128 x (bytes that are not '\n'), accumulated on the multiply-add pipe
-      r.nonnl = not_newline_x128(w0, r.nonnl);
-      r.nonnl = not_newline_x128(w1, r.nonnl);
-      r.nonnl = not_newline_x128(w2, r.nonnl);
-      r.nonnl = not_newline_x128(w3, r.nonnl);
+      r.nonnl = not_newline_x128(w0, r.nonnl, pat.c_nl, pat.c_7f);
+      r.nonnl = not_newline_x128(w1, r.nonnl, pat.c_nl, pat.c_7f);
+      r.nonnl = not_newline_x128(w2, r.nonnl, pat.c_nl, pat.c_7f);
+      r.nonnl = not_newline_x128(w3, r.nonnl, pat.c_nl, pat.c_7f);
     }
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;

@@ -25,6 +25,9 @@ struct Pattern {
   uint32_t anchor;   // m >= 5: pattern index a of the first filter byte (second is a + 4)
   uint32_t rep[4];   // the SIMD-tested bytes replicated into all four lanes of a word
   uint32_t bordered; // pattern overlaps itself (has a proper border) -> greedy resolution needed
+  // 0x0a0a0a0a and 0x7f7f7f7f as run-time values: read from the constant bank they can BOTH be operands of
+  // one LOP3 ((w ^ c_nl) & c_7f); as literals the compiler spends one instruction per immediate
+  uint32_t c_nl, c_7f;
 };
 
 // ---- scan kernel launch arguments ---------------------------------------------------------

@@ -50,6 +50,8 @@ int make_pattern(const uint8_t* p, uint32_t m, Pattern* out) {
   std::memset(&pat, 0, sizeof pat);
   std::memcpy(pat.bytes, p, m);
   pat.m = m;
+  pat.c_nl = 0x0a0a0a0au;
+  pat.c_7f = 0x7f7f7f7fu;
   auto rep = [](uint8_t c) { return 0x01010101u * c; };
   if (m <= 4) {
     pat.nsimd = m;
