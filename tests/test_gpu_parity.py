@@ -260,3 +260,70 @@ def test_large_properties(xs, ctx):
     # shards: the same corpus scanned as two halves with bases equals the whole
     res.free()
     corpus.free()
+
+
+def test_full_size_properties_10gb(xs, ctx):
+    """BASELINE.json sizes (10 GB per GPU): properties that do not need the oracle.
+    (1) the whole corpus scanned at once == the same corpus scanned as three shards of whole reference chunks
+        with byte / line bases (a checksum of checksums over two different launch geometries);
+    (2) vectors are sorted, consistent with the counts, and every sampled result really is a match;
+    (3) the dense direct path (match_byte_offsets of a frequent 3-byte literal) agrees with count-only."""
+    n = (10 * 10 ** 9 + 4095) // 4096 * 4096
+    p = xs.SynthParams.make(2, b"Sherlock", 30.0 / 65536)
+    corpus = ctx.corpus(n)
+    corpus.fill_synth(p)
+    corpus.chunk()
+    bounds = corpus.bounds()
+    assert bounds[-1] == n and bounds.size > 500
+    kinds = xs.COUNT | xs.COUNT_LINES | xs.MATCH_BYTE_OFFSETS | xs.LINE_BYTE_OFFSETS | xs.LINE_INDICES | xs.LINES
+    res = ctx.scan(corpus, b"Sherlock", kinds)
+    whole = {"count": res.count(xs.COUNT), "cl": res.count(xs.COUNT_LINES), "m": res.vector(xs.MATCH_BYTE_OFFSETS),
+             "lo": res.vector(xs.LINE_BYTE_OFFSETS), "li": res.vector(xs.LINE_INDICES), "ls": res.line_spans(),
+             "nl": res.newlines}
+    res.free()
+    assert whole["count"] == whole["m"].size and whole["cl"] == whole["lo"].size == whole["li"].size
+    assert whole["count"] >= whole["cl"] > 0.5 * n / 65536
+    assert (np.diff(whole["m"].astype(np.int64)) >= 8).all()
+    assert (np.diff(whole["lo"].astype(np.int64)) > 0).all() and (np.diff(whole["li"].astype(np.int64)) > 0).all()
+    assert np.array_equal(whole["ls"][0], whole["lo"])
+    for q in whole["m"][:: max(1, whole["m"].size // 64)]:
+        assert corpus.download(int(q), 8).tobytes() == b"Sherlock"
+    for s_, l_, i_ in list(zip(whole["ls"][0], whole["ls"][1], whole["li"]))[:: max(1, whole["li"].size // 32)]:
+        line = corpus.download(int(s_), int(l_) + 1).tobytes()
+        assert b"Sherlock" in line and line.endswith(b"\n") and b"\n" not in line[:-1]
+        assert s_ == 0 or corpus.download(int(s_) - 1, 1)[0] == 10
+    # three shards of whole chunks, each wrapped in place (no copy), with its bases
+    parts = {k: [] for k in ("m", "lo", "li")}
+    line_base = cnt = cl = 0
+    for c0, c1 in xs.shard_chunks(bounds, 3):
+        b0, b1 = (int(bounds[c0 - 1]) if c0 else 0), int(bounds[c1 - 1])
+        if (corpus.device_ptr + b0) % 16 == 0:
+            shard = ctx.wrap(corpus.device_ptr + b0, b1 - b0)   # scanned in place
+        else:                                                    # a wrapped corpus must be 16-byte aligned
+            shard = ctx.corpus(b1 - b0)
+            shard.upload(corpus.download(b0, b1 - b0))
+        shard.set_bounds(bounds[c0:c1] - np.uint64(b0))
+        r = ctx.scan(shard, b"Sherlock", kinds, offset_base=b0)
+        r.rebase(0, line_base)
+        line_base += r.newlines
+        cnt += r.count(xs.COUNT)
+        cl += r.count(xs.COUNT_LINES)
+        parts["m"].append(r.vector(xs.MATCH_BYTE_OFFSETS))
+        parts["lo"].append(r.vector(xs.LINE_BYTE_OFFSETS))
+        parts["li"].append(r.vector(xs.LINE_INDICES))
+        r.free()
+        shard.free()
+    assert cnt == whole["count"] and cl == whole["cl"] and line_base == whole["nl"]
+    for k in parts:
+        assert np.array_equal(np.concatenate(parts[k]), whole[k]), k
+    # dense direct path vs the list-free count path
+    r = ctx.scan(corpus, b"the", xs.MATCH_BYTE_OFFSETS | xs.COUNT)
+    c_list, v = r.count(xs.COUNT), r.vector(xs.MATCH_BYTE_OFFSETS)
+    r.free()
+    r = ctx.scan(corpus, b"the", xs.COUNT)
+    assert r.count(xs.COUNT) == c_list == v.size > n // 100
+    r.free()
+    assert (np.diff(v.astype(np.int64)) >= 3).all()
+    for q in v[:: max(1, v.size // 64)]:
+        assert corpus.download(int(q), 3).tobytes() == b"the"
+    corpus.free()
