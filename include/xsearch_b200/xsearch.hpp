@@ -83,6 +83,7 @@ struct Options {
   int device = 0;
   uint64_t min_chunk = XSG_DEFAULT_MIN_CHUNK;   // v1: chunks of >= 16 MiB, extended through the next '\n'
   uint64_t segment_bytes = 256ull << 20;        // bytes read / copied / scanned per pipeline step
+  bool ignore_case = false;                     // set by the ignore_case overloads of extern_search
 };
 
 // ---- result collector ------------------------------------------------------------------------------
@@ -233,8 +234,10 @@ class Searcher {
     try {
       plan(meta_file_path);
       if (xsg_init(_opt.device, &_ctx) != XSG_OK) throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init"));
+      xsg_scan_opts so{};
+      so.flags = _opt.ignore_case ? XSG_SCAN_IGNORE_CASE : 0u;  // ASCII fold, like v1's tolower processor
       if (xsg_stream_open(_ctx, reinterpret_cast<const uint8_t*>(_pattern.data()), static_cast<uint32_t>(_pattern.size()),
-                          Tag::kind, nullptr, &_stream) != XSG_OK)
+                          Tag::kind, &so, &_stream) != XSG_OK)
         throw std::runtime_error(detail::last_error("xs::extern_search: xsg_stream_open"));
     } catch (...) {
       if (_ctx) xsg_destroy(_ctx);
@@ -579,14 +582,14 @@ template <class Tag>
 std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path,
                                              const std::string& meta_file_path, bool ignore_case, int num_threads,
                                              int max_num_readers, Options opt = {}) {
-  if (ignore_case) throw std::invalid_argument("xs::extern_search: ignore_case is not part of the GPU literal path");
+  opt.ignore_case = ignore_case;
   return std::make_shared<Searcher<Tag>>(pattern, file_path, meta_file_path, num_threads, max_num_readers, opt);
 }
 
 template <class Tag>
 std::shared_ptr<Searcher<Tag>> extern_search(const std::string& pattern, const std::string& file_path, bool ignore_case,
                                              int num_threads = 1, Options opt = {}) {
-  if (ignore_case) throw std::invalid_argument("xs::extern_search: ignore_case is not part of the GPU literal path");
+  opt.ignore_case = ignore_case;
   return std::make_shared<Searcher<Tag>>(pattern, file_path, std::string(), num_threads, 1, opt);
 }
 

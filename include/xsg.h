@@ -69,7 +69,13 @@ typedef struct xsg_scan_opts {
   uint64_t global_offset_base; /* added to every byte offset (shard / segment base)           */
   uint64_t line_index_base;    /* added to every line index ('\n' count before this corpus)   */
   uint64_t occ_capacity;       /* 0 = automatic; max raw occurrences buffered on the device   */
+  uint32_t flags;              /* OR of XSG_SCAN_* flags                                      */
+  uint32_t reserved;
 } xsg_scan_opts;
+/* ignore_case of the reference's one-call API: v1 ran a "tolower" processor over every chunk
+ * (simd::toLower, src/utils/string_utils.cpp:11-33: ASCII A-Z only) and searched the lowered pattern in
+ * the lowered bytes.  Here the fold happens in registers while the bytes are scanned. */
+#define XSG_SCAN_IGNORE_CASE 1u
 
 typedef struct xsg_timings {
   float scan_ms;        /* all device work of the scan (CUDA events on the library's stream) */

@@ -13,6 +13,7 @@
 #include <xsearch/string_search/search_wrappers.h>
 #include <xsearch/string_search/simd_search.h>
 #include <xsearch/types.h>
+#include <xsearch/utils/string_utils.h>
 
 #include <atomic>
 #include <cstdint>
@@ -130,6 +131,8 @@ uint64_t run(const char* buf, const char* pat, uint32_t m, const uint64_t* bound
 XSR_API int64_t xsr_find_next(const char* pat, size_t m, const char* buf, size_t n, size_t shift) {
   return xs::search::simd::findNext(pat, m, buf, n, shift);
 }
+// the reference's own toLower (src/utils/string_utils.cpp:11-33), the v1 ignore_case processor
+XSR_API void xsr_to_lower(char* buf, uint64_t n) { xs::utils::str::simd::toLower(buf, n); }
 XSR_API int64_t xsr_find_next_newline(const char* buf, size_t n, size_t shift) {
   return xs::search::simd::findNextNewLine(buf, n, shift);
 }

@@ -50,6 +50,15 @@ int64_t xso_find_next(const char* pat, size_t m, const char* buf, size_t n, size
   return t < 0 ? -1 : (int64_t)(shift + T) + t;
 }
 
+void xso_to_lower(char* buf, uint64_t n) {
+  /* string_utils.cpp:14-25: signed compares data > 'A'-1 and 'Z'+1 > data, then += 'a'-'A'; the scalar
+   * tail (:28-32) calls std::tolower, which in the "C" locale maps exactly the same 26 bytes */
+  for (uint64_t i = 0; i < n; i++) {
+    signed char c = (signed char)buf[i];
+    if (c > 'A' - 1 && 'Z' + 1 > c) buf[i] = (char)(c + ('a' - 'A'));
+  }
+}
+
 int64_t xso_find_next_newline(const char* buf, size_t n, size_t shift) {
   if (shift > n) return -1; /* simd_search.cpp:298-300 */
   const char* r = (const char*)memchr(buf + shift, '\n', n - shift);

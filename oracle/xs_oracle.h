@@ -36,6 +36,10 @@ int64_t xso_find_next_newline(const char* buf, size_t n, size_t shift);
 uint64_t xso_count_matches(const char* pat, size_t m, const char* buf, size_t n);
 uint64_t xso_count_matching_lines(const char* pat, size_t m, const char* buf, size_t n);
 
+/* reference: src/utils/string_utils.cpp:11-33 (simd::toLower), the v1 "tolower" chunk processor behind
+ * ignore_case: ASCII 'A'..'Z' -> 'a'..'z' in place, every other byte (incl. >= 0x80) unchanged. */
+void xso_to_lower(char* buf, uint64_t n);
+
 /* v1 chunking rule decoded from test/files/sample.meta: each
  * chunk is >= min_chunk bytes and extended through the next '\n' (or to n).
  * Writes exclusive end offsets; returns the number of chunks (0 for n == 0).

@@ -136,3 +136,18 @@ def random_cases(count, seed0, max_n=4000):
                 "plants": int(rng.integers(0, 30)), "end_nl": bool(rng.integers(0, 2))}
         cases.append(case)
     return cases
+
+
+def icase_cases():
+    """Mixed-case corpora for ignore_case (golden outputs: the reference's toLower + its matchers)."""
+    cases = []
+    seed = 5000
+    for pat in ["Sherlock", "sHeRlOcK", "the", "AB", "a", "Z", "needle-NEEDLE-needle-Needle-0032", "\xc9\xfc"]:
+        for n in (0, 33, 500, 3000):
+            seed += 1
+            cases.append({"kind": "planted", "seed": seed, "n": n, "alphabet": "sSHhEeRrLlOoCcKk tT aAbBzZ@[`{\xc9\xe9\xfc\xdc",
+                          "pattern": pat, "nl_prob": 0.04, "min_chunk": 400, "plants": 12, "end_nl": bool(seed & 1)})
+        seed += 1
+        cases.append({"kind": "hazard", "seed": seed, "pattern": pat, "alphabet": "sShHeE rRlL oOcCkK", "chunks": 8,
+                      "body_min": 40, "body_max": 300, "d0": 2, "d_step": 7})
+    return cases

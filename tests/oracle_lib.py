@@ -40,6 +40,9 @@ class Checker:
             fn = getattr(L, p + name)
             fn.restype, fn.argtypes = res, args
             self._f[name] = fn
+        fn = getattr(L, p + "to_lower")
+        fn.restype, fn.argtypes = None, [vp, u64]
+        self._f["to_lower"] = fn
         if prefix == "xso_":
             fn = L.xso_chunk_bounds
             fn.restype, fn.argtypes = u64, [vp, u64, u64, _PU64, u64]
@@ -49,6 +52,14 @@ class Checker:
     def _buf(buf):
         a = np.frombuffer(buf, dtype=np.uint8) if isinstance(buf, (bytes, bytearray)) else buf
         return a, (a.ctypes.data if a.size else 0)
+
+    def to_lower(self, buf) -> np.ndarray:
+        """Copy of buf run through the reference's ignore_case processor (simd::toLower)."""
+        a, _ = self._buf(buf)
+        out = np.ascontiguousarray(a).copy()
+        if out.size:
+            self._f["to_lower"](out.ctypes.data, out.size)
+        return out
 
     def find_next(self, pat: bytes, buf, shift: int) -> int:
         a, addr = self._buf(buf)

@@ -176,6 +176,26 @@ def test_extern_search_edge_files(xsgrep, tmp_path):
 
 
 @pytest.mark.gpu
+def test_extern_search_ignore_case(xsgrep, tmp_path):
+    """The ignore_case overloads (README.md:37, example/grep.cpp:69-77): lines come back with their ORIGINAL bytes."""
+    oracle, _ = oracle_lib.load(build=False)
+    text = (b"Sherlock holmes\nno match here\nSHERLOCK again, sherlock twice\nshErLoCk\n" * 3000)
+    buf = np.frombuffer(text, dtype=np.uint8).copy()
+    path = tmp_path / "mixed.txt"
+    buf.tofile(path)
+    bounds = oracle.chunk_bounds(buf, 65536)
+    lbuf = oracle.to_lower(buf)
+    base = ["--min-chunk", "65536", "--segment-bytes", "262144", "-i"]
+    for tag in TAGS:
+        exp = expected_output(oracle, lbuf, b"sherlock", bounds, tag)
+        if tag == "lines":  # same lines, original spelling
+            st, ln = oracle.lines(lbuf, b"sherlock", bounds)
+            exp = "".join(text[int(s):int(s) + int(l)].decode() + "\n" for s, l in zip(st, ln))
+        assert run_xsgrep(xsgrep, tag, b"SherLOCK", path, base) == exp, tag
+    assert run_xsgrep(xsgrep, "count", b"SherLOCK", path, base[:-1]) == "0\n"
+
+
+@pytest.mark.gpu
 def test_extern_search_errors(xsgrep, tmp_path):
     out = subprocess.run([xsgrep, "abc", str(tmp_path / "missing.txt")], capture_output=True, text=True)
     assert out.returncode == 1 and "cannot open" in out.stderr

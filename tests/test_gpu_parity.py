@@ -327,3 +327,67 @@ def test_full_size_properties_10gb(xs, ctx):
     for q in v[:: max(1, v.size // 64)]:
         assert corpus.download(int(q), 3).tobytes() == b"the"
     corpus.free()
+
+
+def _run_icase(xs, ctx, buf, pat, bounds, exp, tag):
+    corpus = ctx.corpus_from_host(buf, bounds=bounds)
+    try:
+        res = ctx.scan(corpus, pat, all_kinds(xs), ignore_case=True)
+        check_result(xs, res, exp, tag)
+        res.free()
+        res = ctx.scan(corpus, pat, xs.COUNT, ignore_case=True)
+        assert res.count(xs.COUNT) == exp["count"], ("count-only", tag)
+        res.free()
+        res = ctx.scan(corpus, pat, xs.MATCH_BYTE_OFFSETS, ignore_case=True)
+        assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp["match"]), ("direct", tag)
+        res.free()
+    finally:
+        corpus.free()
+
+
+def test_ignore_case_golden_vectors(xs, ctx):
+    """XSG_SCAN_IGNORE_CASE against outputs of the reference's toLower + matchers (tests/golden/icase_vectors.json)."""
+    data = json.load(open(os.path.join(GOLD, "icase_vectors.json")))
+    for v in data["vectors"]:
+        buf, pat, bounds = gen_cases.materialize(v["case"])
+        if buf.size == 0:
+            continue
+        exp = {"count": v["count"], "count_lines": v["count_lines"],
+               "match": np.array(v["match_byte_offsets"], dtype=np.uint64),
+               "line_off": np.array(v["line_byte_offsets"], dtype=np.uint64),
+               "line_idx": np.array(v["line_indices"], dtype=np.uint64),
+               "lines": (np.array([a for a, _ in v["lines"]], dtype=np.uint64),
+                         np.array([b for _, b in v["lines"]], dtype=np.uint64))}
+        _run_icase(xs, ctx, buf, pat, bounds, exp, v["case"])
+
+
+@pytest.mark.parametrize("m", [1, 2, 3, 4, 5, 8, 9, 17, 33, 64])
+def test_ignore_case_differential(xs, ctx, oracle, m):
+    """Mixed-case text, every pattern length class, hits straddling granule / tile edges, streamed path too."""
+    rng = np.random.default_rng(100 + m)
+    base = "Sherlock HOLMES and The Hound of the BaskerVilles went Home [@`{ zZ"
+    pat = base[:m].encode()
+    lpat = oracle.to_lower(np.frombuffer(pat, dtype=np.uint8)).tobytes()
+    for n in (m + 40, 4097, 32768 + 17, 150000):
+        buf = gen_cases._random_text(rng, n, b"sShHeErRlLoOcCkK tT@[`{zZ\n", 0.03)
+        p = np.frombuffer(pat, dtype=np.uint8)
+        for edge in (4096, 32768, 65536, n):
+            for d in (-m - 1, -m + 1, -1, 0, 1):
+                pos = edge + d
+                if 0 <= pos and pos + m <= n:
+                    piece = p.copy()
+                    flip = rng.random(m) < 0.5
+                    alpha = ((piece | 0x20) >= 97) & ((piece | 0x20) <= 122)
+                    piece[flip & alpha] ^= 0x20           # random case of every letter
+                    buf[pos:pos + m] = piece
+        bounds = gen_cases._chunk_bounds(buf, 20000)
+        lbuf = oracle.to_lower(buf)
+        exp = expected(oracle, lbuf, lpat, bounds)
+        _run_icase(xs, ctx, buf, pat, bounds, exp, ("icase", m, n))
+        res = ctx.search_host(buf, None, pat, all_kinds(xs), bounds=bounds, ignore_case=True)
+        check_result(xs, res, exp, ("icase-stream", m, n))
+        res.free()
+        # case-sensitive search of the same buffer must NOT see the folded hits
+        res = ctx.scan(ctx.corpus_from_host(buf, bounds=bounds), pat, xs.COUNT)
+        assert res.count(xs.COUNT) == oracle.count(buf, pat, bounds, False)
+        res.free()

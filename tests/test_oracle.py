@@ -141,3 +141,32 @@ def test_threads_and_chunking(libs):
     four = oracle.match_byte_offsets(buf, pat, bounds, 4)
     assert np.array_equal(one, four) and one.size > 100
     assert oracle.count(buf, pat, bounds, True, 4) == oracle.line_indices(buf, pat, bounds, 3).size
+
+
+def test_to_lower_matches_reference(libs):
+    """simd::toLower (string_utils.cpp:11-33): only ASCII A-Z move, at every alignment / tail length."""
+    oracle, ref = libs
+    allb = np.arange(256, dtype=np.uint8)
+    want = allb.copy()
+    want[65:91] += 32
+    for n in (0, 1, 31, 32, 33, 63, 64, 65, 256, 700):
+        buf = np.resize(allb, n)
+        assert np.array_equal(oracle.to_lower(buf), np.resize(want, n)), n
+        if ref is not None:
+            assert np.array_equal(ref.to_lower(buf), np.resize(want, n)), n
+
+
+def test_golden_ignore_case_vectors(libs):
+    """ignore_case = the reference's toLower over chunk and pattern, then its matchers (committed outputs)."""
+    oracle, _ = libs
+    data = json.load(open(os.path.join(GOLD, "icase_vectors.json")))
+    assert len(data["vectors"]) >= 40 and sum(v["count"] for v in data["vectors"]) > 300
+    for v in data["vectors"]:
+        buf, pat, bounds = gen_cases.materialize(v["case"])
+        lbuf, lpat = oracle.to_lower(buf), oracle.to_lower(np.frombuffer(pat, dtype=np.uint8)).tobytes()
+        assert oracle.count(lbuf, lpat, bounds, False) == v["count"], v["case"]
+        assert oracle.count(lbuf, lpat, bounds, True) == v["count_lines"], v["case"]
+        assert [int(x) for x in oracle.match_byte_offsets(lbuf, lpat, bounds)] == v["match_byte_offsets"], v["case"]
+        assert [int(x) for x in oracle.line_indices(lbuf, lpat, bounds)] == v["line_indices"], v["case"]
+        st, ln = oracle.lines(lbuf, lpat, bounds)
+        assert [[int(a), int(b)] for a, b in zip(st, ln)] == v["lines"], v["case"]

@@ -13,6 +13,8 @@ import os
 import re
 import sys
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 REF = "/root/reference"
@@ -95,7 +97,41 @@ def main():
         })
     json.dump({"generator": "tools/make_golden.py via oracle/_ref/libxsref.so (reference @ 86641bb)", "vectors": vecs},
               open(os.path.join(GOLD, "ref_vectors.json"), "w"))
-    print("golden: %d KAT groups, %d reference vectors" % (len(kat) - 1, len(vecs)))
+    # ignore_case: the reference's toLower processor (src/utils/string_utils.cpp:11-33) over buffer and pattern,
+    # then its unmodified matchers
+    ivecs = []
+    for case in gen_cases.icase_cases():
+        buf, pat, bounds = gen_cases.materialize(case)
+        lbuf, lpat = ref.to_lower(buf), ref.to_lower(np.frombuffer(pat, dtype=np.uint8)).tobytes()
+        st, ln = ref.lines(lbuf, lpat, bounds)
+        ivecs.append({
+            "case": case,
+            "count": int(ref.count(lbuf, lpat, bounds, False)),
+            "count_lines": int(ref.count(lbuf, lpat, bounds, True)),
+            "match_byte_offsets": [int(x) for x in ref.match_byte_offsets(lbuf, lpat, bounds)],
+            "line_byte_offsets": [int(x) for x in ref.line_byte_offsets(lbuf, lpat, bounds)],
+            "line_indices": [int(x) for x in ref.line_indices(lbuf, lpat, bounds)],
+            "lines": [[int(a), int(b)] for a, b in zip(st, ln)],
+        })
+    json.dump({"generator": "tools/make_golden.py: xs::utils::str::simd::toLower + matchers of oracle/_ref/libxsref.so",
+               "vectors": ivecs}, open(os.path.join(GOLD, "icase_vectors.json"), "w"))
+    # chunk table of the reference's meta-file fixture (format: SURVEY.md 3.5)
+    import struct
+    raw = open(os.path.join(REF, "test/files/sample.meta"), "rb").read()
+    pos, chunks = 4, []
+    while pos < len(raw):
+        oo, ao, osz, asz, nm = struct.unpack_from("<5Q", raw, pos)
+        pos += 40
+        first = struct.unpack_from("<2Q", raw, pos) if nm else (0, 0)
+        last = struct.unpack_from("<2Q", raw, pos + 16 * (nm - 1)) if nm else (0, 0)
+        pos += 16 * nm
+        chunks.append(dict(original_offset=oo, actual_offset=ao, original_size=osz, actual_size=asz, n_map=nm,
+                           first_mapping=list(first), last_mapping=list(last)))
+    json.dump({"source": "test/files/sample.meta of the reference (3 060 484 bytes): chunk table and first/last line "
+                         "mapping of each chunk", "compression_type": struct.unpack_from("<I", raw, 0)[0],
+               "original_size": chunks[-1]["original_offset"] + chunks[-1]["original_size"], "chunks": chunks},
+              open(os.path.join(GOLD, "sample_meta_chunks.json"), "w"), indent=1)
+    print("golden: %d KAT groups, %d reference vectors, %d ignore-case vectors" % (len(kat) - 1, len(vecs), len(ivecs)))
 
 
 if __name__ == "__main__":

@@ -28,6 +28,7 @@ MATCH_BYTE_OFFSETS = 1 << 2
 LINE_BYTE_OFFSETS = 1 << 3
 LINE_INDICES = 1 << 4
 LINES = 1 << 5
+SCAN_IGNORE_CASE = 1  # xsg_scan_opts.flags
 
 # the reference's tag names (README.md:72-81; tests also spell xs::count as count_matches)
 TAGS = {
@@ -60,7 +61,8 @@ class XsgError(RuntimeError):
 
 
 class ScanOpts(C.Structure):
-    _fields_ = [("global_offset_base", C.c_uint64), ("line_index_base", C.c_uint64), ("occ_capacity", C.c_uint64)]
+    _fields_ = [("global_offset_base", C.c_uint64), ("line_index_base", C.c_uint64), ("occ_capacity", C.c_uint64),
+                ("flags", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class Timings(C.Structure):

@@ -16,7 +16,7 @@ from typing import Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from . import (COUNT, COUNT_LINES, DEFAULT_MIN_CHUNK, LINE_BYTE_OFFSETS, LINE_INDICES, LINES,
+from . import (SCAN_IGNORE_CASE, COUNT, COUNT_LINES, DEFAULT_MIN_CHUNK, LINE_BYTE_OFFSETS, LINE_INDICES, LINES,
                MATCH_BYTE_OFFSETS, SYNTH_BLOCK, TAGS, ScanOpts, SynthParams, Timings, XsgError, _check, lib)
 
 _PU64 = C.POINTER(C.c_uint64)
@@ -111,21 +111,21 @@ class Context:
 
     # -- searches ---------------------------------------------------------------------------
     def scan(self, corpus: "Corpus", pattern: bytes, kinds: int, offset_base: int = 0, line_index_base: int = 0,
-             occ_capacity: int = 0) -> "Result":
-        opts = ScanOpts(offset_base, line_index_base, occ_capacity)
+             occ_capacity: int = 0, ignore_case: bool = False) -> "Result":
+        opts = ScanOpts(offset_base, line_index_base, occ_capacity, SCAN_IGNORE_CASE if ignore_case else 0, 0)
         h = C.c_void_p()
         _check(lib.xsg_scan(self._h, corpus._h, pattern, len(pattern), kinds, C.byref(opts), C.byref(h)))
         return Result(h, kinds)
 
     def search_host(self, buf, n_bytes: Optional[int], pattern: bytes, kinds: int,
                     bounds: Optional[np.ndarray] = None, min_chunk: int = DEFAULT_MIN_CHUNK,
-                    offset_base: int = 0, line_index_base: int = 0) -> "Result":
+                    offset_base: int = 0, line_index_base: int = 0, ignore_case: bool = False) -> "Result":
         """buf: numpy uint8 array or raw address (int) of a host buffer (pinned for full speed)."""
         if isinstance(buf, np.ndarray):
             addr, n = buf.ctypes.data, int(buf.size)
         else:
             addr, n = int(buf), int(n_bytes)
-        opts = ScanOpts(offset_base, line_index_base, 0)
+        opts = ScanOpts(offset_base, line_index_base, 0, SCAN_IGNORE_CASE if ignore_case else 0, 0)
         h = C.c_void_p()
         bp, nb = (None, 0) if bounds is None else (_u64ptr(bounds), int(bounds.size))
         _check(lib.xsg_search_host(self._h, C.c_void_p(addr), n, bp, nb, min_chunk, pattern, len(pattern), kinds,
@@ -272,12 +272,12 @@ class Searcher:
 
     def __init__(self, kind: int, pattern: bytes, file_path: str, meta_file: Optional[str] = None,
                  num_threads: int = 1, max_num_readers: int = 1, device: int = 0,
-                 min_chunk: int = DEFAULT_MIN_CHUNK):
+                 min_chunk: int = DEFAULT_MIN_CHUNK, ignore_case: bool = False):
         if isinstance(pattern, str):
             pattern = pattern.encode()
         self.kind, self.pattern, self.file_path = kind, pattern, file_path
         self._size, self._values, self._error = 0, [], None
-        self._device, self._min_chunk = device, min_chunk
+        self._device, self._min_chunk, self._ignore_case = device, min_chunk, ignore_case
         self._thread = threading.Thread(target=self._run, daemon=True)
         self._thread.start()
 
@@ -286,7 +286,8 @@ class Searcher:
             data = np.fromfile(self.file_path, dtype=np.uint8)
             ctx = Context(self._device)
             try:
-                res = ctx.search_host(data, None, self.pattern, self.kind, min_chunk=self._min_chunk)
+                res = ctx.search_host(data, None, self.pattern, self.kind, min_chunk=self._min_chunk,
+                                      ignore_case=self._ignore_case)
                 self._size = res.count(self.kind)
                 if self.kind == LINES:
                     st, ln = res.line_spans()
@@ -319,9 +320,7 @@ def extern_search(tag, pattern, file_path: str, meta_file: Optional[str] = None,
                   max_num_readers: int = 1, ignore_case: bool = False, **kw) -> Searcher:
     """xs::extern_search<Tag>(pattern, file, meta_file, num_threads, max_num_readers)."""
     kind = TAGS[tag] if isinstance(tag, str) else int(tag)
-    if ignore_case:
-        raise XsgError(-2, "ignore_case is not part of the GPU literal path")
-    return Searcher(kind, pattern, file_path, meta_file, num_threads, max_num_readers, **kw)
+    return Searcher(kind, pattern, file_path, meta_file, num_threads, max_num_readers, ignore_case=ignore_case, **kw)
 
 
 def shard_chunks(bounds: np.ndarray, world: int) -> List[Tuple[int, int]]:

@@ -34,6 +34,11 @@ __device__ __forceinline__ uint32_t keep_lanes(uint32_t w, long long valid) {
 
 // full compare of the pattern at corpus position q (slow path of the m >= 5 filter)
 __device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t q, const Pattern& pat) {
+  if (pat.icase) {
+    for (uint32_t k = 0; k < pat.m; ++k)
+      if (fold_byte(buf[q + k]) != pat.bytes[k]) return false;
+    return true;
+  }
   for (uint32_t k = 0; k < pat.m; ++k)
     if (buf[q + k] != pat.bytes[k]) return false;
   return true;
@@ -88,7 +93,7 @@ __device__ __forceinline__ void load_granule(const uint8_t* __restrict__ buf, ui
 
 // Phase 1 for one warp granule: classify, (verify), count.  NS: 1..4 = exact compare of m = NS
 // consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification.
-template <int NS, bool EMIT, bool NL>
+template <int NS, bool EMIT, bool NL, bool ICASE>
 __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
                                                  uint64_t gran_off, int lane, const uint4 (&v)[kRows], uint32_t ext,
                                                  LaneResult& r) {
@@ -103,10 +108,15 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 
 #pragma unroll
   for (int u = 0; u < kRows; ++u) {
-    const uint32_t w0 = v[u].x, w1 = v[u].y, w2 = v[u].z, w3 = v[u].w;
+    // ignore case: ASCII upper -> lower in registers ('\n' is not touched, so the newline count may use either)
+    const uint32_t w0 = ICASE ? fold_word(v[u].x) : v[u].x, w1 = ICASE ? fold_word(v[u].y) : v[u].y;
+    const uint32_t w2 = ICASE ? fold_word(v[u].z) : v[u].z, w3 = ICASE ? fold_word(v[u].w) : v[u].w;
     // halo word: lane l takes word 0 of lane l+1; lane 31 takes word 0 of the next row (held by lane 0)
     uint32_t send = w0;
-    if (lane == 0) send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
+    if (lane == 0) {
+      send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
+      if (ICASE) send = fold_word(send);
+    }
     const uint32_t w4 = __shfl_sync(kFull, send, (lane + 1) & 31);
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
@@ -177,7 +187,7 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 // No inter-warp communication at all: each warp owns its granule and writes its own counters.  With
 // MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
 // an occurrence, so pass 2 never touches the corpus again.
-template <int NS, bool NL, bool MASK>
+template <int NS, bool NL, bool MASK, bool ICASE>
 __global__ void __launch_bounds__(kThreads, 3)
 count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
@@ -188,7 +198,7 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   uint32_t ext;
   load_granule(a.buf, a.n, gran_off, lane, v, ext);
   LaneResult r;
-  classify_granule<NS, MASK, NL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
+  classify_granule<NS, MASK, NL, ICASE>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
   if (NL) {
     const uint32_t s = warp_sum(r.nonnl) >> 7;
     if (lane == 0) a.nl_granule[g] = kGranuleBytes - s;
@@ -266,30 +276,35 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   }
 }
 
-template <int NS>
+template <int NS, bool ICASE>
 cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
   if (masks) {
-    if (newlines) count_kernel<NS, true, true><<<grid, block, 0, s>>>(pat, a);
-    else count_kernel<NS, false, true><<<grid, block, 0, s>>>(pat, a);
+    if (newlines) count_kernel<NS, true, true, ICASE><<<grid, block, 0, s>>>(pat, a);
+    else count_kernel<NS, false, true, ICASE><<<grid, block, 0, s>>>(pat, a);
   } else {
-    if (newlines) count_kernel<NS, true, false><<<grid, block, 0, s>>>(pat, a);
-    else count_kernel<NS, false, false><<<grid, block, 0, s>>>(pat, a);
+    if (newlines) count_kernel<NS, true, false, ICASE><<<grid, block, 0, s>>>(pat, a);
+    else count_kernel<NS, false, false, ICASE><<<grid, block, 0, s>>>(pat, a);
   }
   return cudaGetLastError();
+}
+
+template <bool ICASE>
+cudaError_t launch_count_ic(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
+  switch (pat.m) {
+    case 1: return launch_count_ns<1, ICASE>(pat, a, newlines, masks, s);
+    case 2: return launch_count_ns<2, ICASE>(pat, a, newlines, masks, s);
+    case 3: return launch_count_ns<3, ICASE>(pat, a, newlines, masks, s);
+    case 4: return launch_count_ns<4, ICASE>(pat, a, newlines, masks, s);
+    default: return launch_count_ns<5, ICASE>(pat, a, newlines, masks, s);
+  }
 }
 
 }  // namespace
 
 cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
-  switch (pat.m) {
-    case 1: return launch_count_ns<1>(pat, a, newlines, masks, s);
-    case 2: return launch_count_ns<2>(pat, a, newlines, masks, s);
-    case 3: return launch_count_ns<3>(pat, a, newlines, masks, s);
-    case 4: return launch_count_ns<4>(pat, a, newlines, masks, s);
-    default: return launch_count_ns<5>(pat, a, newlines, masks, s);
-  }
+  return pat.icase ? launch_count_ic<true>(pat, a, newlines, masks, s) : launch_count_ic<false>(pat, a, newlines, masks, s);
 }
 
 cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {

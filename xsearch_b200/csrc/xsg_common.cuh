@@ -28,6 +28,7 @@ struct Pattern {
   // 0x0a0a0a0a and 0x7f7f7f7f as run-time values: read from the constant bank they can BOTH be operands of
   // one LOP3 ((w ^ c_nl) & c_7f); as literals the compiler spends one instruction per immediate
   uint32_t c_nl, c_7f;
+  uint32_t icase;    // ignore case: bytes[] is already lowered, corpus bytes are folded (ASCII A-Z) before every compare
 };
 
 // ---- scan kernel launch arguments ---------------------------------------------------------
@@ -46,7 +47,7 @@ struct ScanArgs {
 };
 
 // launchers implemented in scan_kernel.cu
-cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s);
+cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s);  // pat.icase selects the folding variant
 cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s);
 
 // ---- list-domain (post) kernels, list_kernels.cu -------------------------------------------
@@ -105,6 +106,15 @@ __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
   uint32_t r;
   asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
   return r;
+}
+
+// ASCII upper -> lower of one byte / of the four byte lanes of a word (simd::toLower, string_utils.cpp:11-33)
+__host__ __device__ __forceinline__ uint8_t fold_byte(uint8_t c) { return (uint8_t)(c - 'A') < 26u ? (uint8_t)(c | 0x20) : c; }
+__device__ __forceinline__ uint32_t fold_word(uint32_t w) {
+  const uint32_t t = w & 0x7f7f7f7fu;
+  const uint32_t ge = t + 0x3f3f3f3fu;  // bit 7 of a lane: low seven bits >= 'A'
+  const uint32_t gt = t + 0x25252525u;  // bit 7 of a lane: low seven bits >  'Z'
+  return w | (((ge & ~gt & ~w) & 0x80808080u) >> 2);
 }
 
 constexpr uint32_t k7F = 0x7f7f7f7fu;

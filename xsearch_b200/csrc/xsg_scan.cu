@@ -36,7 +36,13 @@ uint32_t byte_weight(uint8_t c) {
   return 1;
 }
 
-int make_pattern(const uint8_t* p, uint32_t m, Pattern* out) {
+int make_pattern(const uint8_t* p_in, uint32_t m, bool icase, Pattern* out) {
+  uint8_t lowered[XSG_MAX_PATTERN];
+  const uint8_t* p = p_in;
+  if (p_in && icase && m >= 1 && m <= XSG_MAX_PATTERN) {  // the reference lowers the pattern as well
+    for (uint32_t i = 0; i < m; ++i) lowered[i] = fold_byte(p_in[i]);
+    p = lowered;
+  }
   if (!p || m == 0 || m > XSG_MAX_PATTERN) {
     set_error("pattern length must be 1..64");
     return XSG_ERR_ARG;
@@ -50,6 +56,7 @@ int make_pattern(const uint8_t* p, uint32_t m, Pattern* out) {
   std::memset(&pat, 0, sizeof pat);
   std::memcpy(pat.bytes, p, m);
   pat.m = m;
+  pat.icase = icase ? 1 : 0;
   pat.c_nl = 0x0a0a0a0au;
   pat.c_7f = 0x7f7f7f7fu;
   auto rep = [](uint8_t c) { return 0x01010101u * c; };
