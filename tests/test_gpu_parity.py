@@ -391,3 +391,49 @@ def test_ignore_case_differential(xs, ctx, oracle, m):
         res = ctx.scan(ctx.corpus_from_host(buf, bounds=bounds), pat, xs.COUNT)
         assert res.count(xs.COUNT) == oracle.count(buf, pat, bounds, False)
         res.free()
+
+
+def test_stream_interface_parts_and_errors(xs, ctx, oracle):
+    """xsg_stream_*: parts appear one push late, in file order, with global bases; contract violations are errors."""
+    p = xs.SynthParams.make(12, b"Sherlock", 30.0 / 4096)
+    host = xs.synth_host(4096 * 600, p)
+    bounds = oracle.chunk_bounds(host, 150000)
+    exp_m = oracle.match_byte_offsets(host, b"Sherlock", bounds)
+    exp_i = oracle.line_indices(host, b"Sherlock", bounds)
+    st = xs.Stream(ctx, b"Sherlock", xs.MATCH_BYTE_OFFSETS | xs.LINE_INDICES | xs.COUNT)
+    segs, got_m, got_i = [], [], []
+    for c0 in range(0, bounds.size, 3):                        # three chunks per segment
+        c1 = min(c0 + 3, bounds.size)
+        b0 = int(bounds[c0 - 1]) if c0 else 0
+        seg = host[b0:int(bounds[c1 - 1])]
+        segs.append(seg)
+        t = st.push(seg, bounds[c0:c1] - np.uint64(b0))
+        assert t == len(segs) - 1
+        assert st.num_parts() == len(segs) - 1                  # the previous segment was scanned inside this push
+        st.wait_copied(t)
+    for part in range(st.num_parts()):
+        got_m.append(st.part_vector(part, xs.MATCH_BYTE_OFFSETS))
+        got_i.append(st.part_vector(part, xs.LINE_INDICES))
+    res = st.close()
+    assert res.count(xs.COUNT) == exp_m.size
+    assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp_m) and np.array_equal(res.vector(xs.LINE_INDICES), exp_i)
+    assert np.array_equal(np.concatenate(got_m), exp_m[:sum(v.size for v in got_m)])
+    assert np.array_equal(np.concatenate(got_i), exp_i[:sum(v.size for v in got_i)])
+    res.free()
+    # errors: bounds not ending at the segment size / not newline-aligned / a segment after an unterminated one
+    st = xs.Stream(ctx, b"x", xs.COUNT)
+    seg = np.frombuffer(b"ab\ncd\nef", dtype=np.uint8).copy()
+    with pytest.raises(xs.XsgError):
+        st.push(seg, np.array([3, 6], dtype=np.uint64))
+    with pytest.raises(xs.XsgError):
+        st.push(seg, np.array([2, 8], dtype=np.uint64))
+    st.push(seg, np.array([3, 6, 8], dtype=np.uint64))          # unterminated end: allowed once, as the last segment
+    with pytest.raises(xs.XsgError):
+        st.push(seg, np.array([8], dtype=np.uint64))
+    res = st.close()
+    assert res.count(xs.COUNT) == 0
+    res.free()
+    st = xs.Stream(ctx, b"x", xs.COUNT)
+    st.abort()
+    with pytest.raises(xs.XsgError):
+        xs.Stream(ctx, b"a\nb", xs.COUNT)

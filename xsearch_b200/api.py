@@ -133,6 +133,60 @@ class Context:
         return Result(h, kinds)
 
 
+class Stream:
+    """A streamed search (xsg_stream): push segments of whole reference chunks, read result parts as they
+    finish, close() for the complete Result.  Mirrors the reference's reader -> searcher -> result loop."""
+
+    def __init__(self, ctx: Context, pattern: bytes, kinds: int, offset_base: int = 0, line_index_base: int = 0,
+                 ignore_case: bool = False):
+        opts = ScanOpts(offset_base, line_index_base, 0, SCAN_IGNORE_CASE if ignore_case else 0, 0)
+        h = C.c_void_p()
+        _check(lib.xsg_stream_open(ctx._h, pattern, len(pattern), kinds, C.byref(opts), C.byref(h)))
+        self._h, self.kinds = h, kinds
+
+    def push(self, buf: np.ndarray, rel_bounds: np.ndarray) -> int:
+        """buf must stay alive and unchanged until wait_copied(ticket) returned."""
+        b = np.ascontiguousarray(rel_bounds, dtype=np.uint64)
+        t = C.c_uint64()
+        _check(lib.xsg_stream_push(self._h, C.c_void_p(buf.ctypes.data), int(buf.size), _u64ptr(b), int(b.size),
+                                   C.byref(t)))
+        return int(t.value)
+
+    def wait_copied(self, ticket: int) -> None:
+        _check(lib.xsg_stream_wait_copied(self._h, ticket))
+
+    def num_parts(self) -> int:
+        return int(lib.xsg_result_num_parts(lib.xsg_stream_result(self._h)))
+
+    def part_count(self, part: int, kind: int) -> int:
+        return int(lib.xsg_result_part_count(lib.xsg_stream_result(self._h), part, kind))
+
+    def part_vector(self, part: int, kind: int) -> np.ndarray:
+        res = lib.xsg_stream_result(self._h)
+        n = int(lib.xsg_result_part_count(res, part, kind))
+        out = np.empty(n, dtype=np.uint64)
+        if n:
+            _check(lib.xsg_result_part_copy(res, part, kind, _u64ptr(out), n))
+        return out
+
+    def close(self) -> "Result":
+        h = C.c_void_p()
+        st, self._h = self._h, None
+        _check(lib.xsg_stream_close(st, C.byref(h)))
+        return Result(h, self.kinds)
+
+    def abort(self) -> None:
+        if self._h:
+            lib.xsg_stream_abort(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.abort()
+        except Exception:
+            pass
+
+
 class Corpus:
     """Device-resident bytes + reference-chunk bounds (xsg_corpus)."""
 
