@@ -152,6 +152,59 @@ def test_pattern_lengths_and_tile_edges(xs, ctx, oracle, m):
         run_case(xs, ctx, oracle, buf, pat, bounds, ("edges", m, n))
 
 
+@pytest.mark.parametrize("pat", [b"aba", b"abab", b"aa", b"that", b"abcab", b"abcabcab", b"going-go", b"x" * 9,
+                                 b"needle-needle-needle-needle-0032-needle"])
+def test_bordered_count_without_list(xs, ctx, oracle, pat):
+    """xs::count of a pattern that can overlap itself: pass 1 detects overlapping occurrences on the fly; without any
+    the count needs no occurrence list (4 launches), with a single overlapping pair -- wherever it lies relative
+    to lane, row, granule and tile edges -- the list path takes over.  Both must equal the oracle."""
+    m = len(pat)
+    p = np.frombuffer(pat, dtype=np.uint8)
+    fail = [0] * (m + 1)
+    k = 0
+    for i in range(1, m):
+        while k and pat[i] != pat[k]:
+            k = fail[k]
+        if pat[i] == pat[k]:
+            k += 1
+        fail[i + 1] = k
+    periods, b = [], fail[m]
+    while b:
+        periods.append(m - b)
+        b = fail[b]
+    assert periods
+    rng = np.random.default_rng(m)
+    n = 3 * 32768 + 1000
+    base = gen_cases._random_text(rng, n, b"cdefgh \n" if m > 2 else b"cdefgh\n", 0.02)
+    for pos in range(100, n - 2 * m, 997):           # non-overlapping occurrences, nothing near the probe sites
+        if not any(abs(pos - e) < 200 for e in (4096, 32768, 65536)) and 10 not in base[pos:pos + m]:
+            base[pos:pos + m] = p
+    base[4096 - 200:4096 + 200][base[4096 - 200:4096 + 200] == 10] = 32
+    base[32768 - 200:32768 + 200][base[32768 - 200:32768 + 200] == 10] = 32
+    bounds = gen_cases._chunk_bounds(base, 30000)
+    corpus = ctx.corpus_from_host(base, bounds=bounds)
+    res = ctx.scan(corpus, pat, xs.COUNT)
+    assert res.count(xs.COUNT) == oracle.count(base, pat, bounds, False) > 30
+    assert res.timings().kernel_launches == 4, "no overlap anywhere: list-free path"
+    res.free()
+    corpus.free()
+    for edge in (16 * 7, 512, 512 * 5, 4096, 32768):
+        for d in periods[:3]:
+            for shift in sorted({0, 1, d - 1, d, d + 1, m - 1, m, m + d - 1}):
+                buf = base.copy()
+                q = edge - shift                      # first occurrence at q, its overlapping partner at q + d
+                if q < 0:
+                    continue
+                piece = np.concatenate([p[:d], p])
+                buf[q:q + piece.size] = piece
+                corpus = ctx.corpus_from_host(buf, bounds=bounds)
+                res = ctx.scan(corpus, pat, xs.COUNT)
+                assert res.count(xs.COUNT) == oracle.count(buf, pat, bounds, False), (pat, edge, d, shift)
+                assert res.timings().kernel_launches > 4, ("overlap must be seen", pat, edge, d, shift)
+                res.free()
+                corpus.free()
+
+
 def test_special_bytes_and_lines(xs, ctx, oracle):
     rng = np.random.default_rng(5)
     # CRLF, empty lines, bytes >= 0x80, a NUL in the pattern, no trailing newline, one very long line

@@ -16,7 +16,7 @@ import os
 from typing import Iterator, List, Optional, Sequence
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libxsg.so")
+LIB_PATH = os.environ.get("XSG_LIB") or os.path.join(_HERE, "libxsg.so")  # XSG_LIB: A/B runs of a development build
 
 MAX_PATTERN = 64
 DEFAULT_MIN_CHUNK = 16777216

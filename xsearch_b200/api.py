@@ -115,7 +115,7 @@ class Context:
         opts = ScanOpts(offset_base, line_index_base, occ_capacity, SCAN_IGNORE_CASE if ignore_case else 0, 0)
         h = C.c_void_p()
         _check(lib.xsg_scan(self._h, corpus._h, pattern, len(pattern), kinds, C.byref(opts), C.byref(h)))
-        return Result(h, kinds)
+        return Result(h, kinds, self)
 
     def search_host(self, buf, n_bytes: Optional[int], pattern: bytes, kinds: int,
                     bounds: Optional[np.ndarray] = None, min_chunk: int = DEFAULT_MIN_CHUNK,
@@ -130,7 +130,7 @@ class Context:
         bp, nb = (None, 0) if bounds is None else (_u64ptr(bounds), int(bounds.size))
         _check(lib.xsg_search_host(self._h, C.c_void_p(addr), n, bp, nb, min_chunk, pattern, len(pattern), kinds,
                                    C.byref(opts), C.byref(h)))
-        return Result(h, kinds)
+        return Result(h, kinds, self)
 
 
 class Stream:
@@ -142,7 +142,7 @@ class Stream:
         opts = ScanOpts(offset_base, line_index_base, 0, SCAN_IGNORE_CASE if ignore_case else 0, 0)
         h = C.c_void_p()
         _check(lib.xsg_stream_open(ctx._h, pattern, len(pattern), kinds, C.byref(opts), C.byref(h)))
-        self._h, self.kinds = h, kinds
+        self._h, self.kinds, self.ctx = h, kinds, ctx
 
     def push(self, buf: np.ndarray, rel_bounds: np.ndarray) -> int:
         """buf must stay alive and unchanged until wait_copied(ticket) returned."""
@@ -173,7 +173,7 @@ class Stream:
         h = C.c_void_p()
         st, self._h = self._h, None
         _check(lib.xsg_stream_close(st, C.byref(h)))
-        return Result(h, self.kinds)
+        return Result(h, self.kinds, self.ctx)
 
     def abort(self) -> None:
         if self._h:
@@ -195,7 +195,8 @@ class Corpus:
 
     def free(self) -> None:
         if self._h:
-            lib.xsg_corpus_free(self._h)
+            if self.ctx._h:  # see Result.free
+                lib.xsg_corpus_free(self._h)
             self._h = None
 
     def __del__(self):
@@ -238,12 +239,14 @@ class Corpus:
 class Result:
     """Device-resident result vectors of one search (xsg_result)."""
 
-    def __init__(self, handle, kinds: int):
-        self._h, self.kinds = handle, kinds
+    def __init__(self, handle, kinds: int, ctx: Optional[Context] = None):
+        self._h, self.kinds, self.ctx = handle, kinds, ctx
 
     def free(self) -> None:
         if self._h:
-            lib.xsg_result_free(self._h)
+            # a result outliving its (already destroyed) context must not touch the dangling xsg_ctx
+            if self.ctx is None or self.ctx._h:
+                lib.xsg_result_free(self._h)
             self._h = None
 
     def __del__(self):

@@ -48,8 +48,8 @@ __device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t
 // operations: bit 7 of ((w ^ c) & 0x7f) + 0x7f is set iff the low seven bits differ from c; bit 7 of
 // w itself differs from c iff it is set (c = 0x0a has it clear), so the xor is not needed for the
 // final OR.  The four 0x80 flags are summed by one dp4a instead of popc + add.
-__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc, uint32_t c_nl, uint32_t c_7f) {
-  const uint32_t b = ((w ^ c_nl) & c_7f) + k7F;
+__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc, uint32_t c_nl, uint32_t c_7f, uint32_t one) {
+  const uint32_t b = add_on_fma_pipe((w ^ c_nl) & c_7f, one, c_7f);
   return __dp4a((b | w) & k80, k01, acc);
 }
 
@@ -57,6 +57,7 @@ struct LaneResult {
   uint32_t mask[kRows / 2];  // EMIT: 16 occurrence bits per row, two rows per register
   uint32_t cnt;              // occurrences owned by this lane
   uint32_t nonnl;            // 128 x bytes that are not '\n' (zero padding included)
+  uint32_t ovl;              // OVL: non-zero when an occurrence of this lane overlaps a later one
 };
 
 // Loads one warp granule: 8 independent coalesced 16-byte loads per thread (+ the halo word in lane 0).
@@ -93,7 +94,9 @@ __device__ __forceinline__ void load_granule(const uint8_t* __restrict__ buf, ui
 
 // Phase 1 for one warp granule: classify, (verify), count.  NS: 1..4 = exact compare of m = NS
 // consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification.
-template <int NS, bool EMIT, bool NL, bool ICASE>
+// OVL (bordered patterns, xs::count without a list): additionally report whether ANY two occurrences overlap.
+// Two occurrences q < q' overlap only at a distance q' - q that is a period of the pattern (pat.periods).
+template <int NS, bool EMIT, bool NL, bool ICASE, bool OVL>
 __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
                                                  uint64_t gran_off, int lane, const uint4 (&v)[kRows], uint32_t ext,
                                                  LaneResult& r) {
@@ -102,6 +105,7 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 
   r.cnt = 0;
   r.nonnl = 0;
+  r.ovl = 0;
 #pragma unroll
   for (int i = 0; i < kRows / 2; ++i) r.mask[i] = 0;
   const long long last_q = (long long)n - (long long)pat.m;  // last valid occurrence start
@@ -121,10 +125,10 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
     if (NL) {  // 128 x (bytes that are not '\n'), accumulated on the multiply-add pipe
-      r.nonnl = not_newline_x128(w0, r.nonnl, pat.c_nl, pat.c_7f);
-      r.nonnl = not_newline_x128(w1, r.nonnl, pat.c_nl, pat.c_7f);
-      r.nonnl = not_newline_x128(w2, r.nonnl, pat.c_nl, pat.c_7f);
-      r.nonnl = not_newline_x128(w3, r.nonnl, pat.c_nl, pat.c_7f);
+      r.nonnl = not_newline_x128(w0, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
+      r.nonnl = not_newline_x128(w1, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
+      r.nonnl = not_newline_x128(w2, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
+      r.nonnl = not_newline_x128(w3, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
     }
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
@@ -137,10 +141,11 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
         z2 |= __funnelshift_r(w2, w3, 8 * k) ^ pat.rep[k];
         z3 |= __funnelshift_r(w3, w4, 8 * k) ^ pat.rep[k];
       }
-      f0 = zero_lanes(z0);
-      f1 = zero_lanes(z1);
-      f2 = zero_lanes(z2);
-      f3 = zero_lanes(z3);
+      // exact zero test per byte lane, its addition issued on the multiply-add pipe (see add_on_fma_pipe)
+      f0 = ~(add_on_fma_pipe(z0 & k7F, pat.one, pat.c_7f) | z0) & k80;
+      f1 = ~(add_on_fma_pipe(z1 & k7F, pat.one, pat.c_7f) | z1) & k80;
+      f2 = ~(add_on_fma_pipe(z2 & k7F, pat.one, pat.c_7f) | z2) & k80;
+      f3 = ~(add_on_fma_pipe(z3 & k7F, pat.one, pat.c_7f) | z3) & k80;
       if (partial) {  // zero padding / bytes behind n must not match
         const long long lim = last_q + 1 - (long long)pos0;
         f0 = keep_lanes(f0, lim);
@@ -149,6 +154,27 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
         f3 = keep_lanes(f3, lim - 12);
       }
       r.cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+      if (OVL) {
+        // occurrence flags sit at bit 7 of their byte lane: the flag of position j + d, shifted down by d lanes,
+        // meets the flag of position j.  The word behind this lane's 16 bytes is word 0 of the next lane; for
+        // lane 31 that is another row or granule, so its last word is checked byte-wise instead.
+        uint32_t f4 = __shfl_sync(kFull, f0, (lane + 1) & 31);
+        if (lane == 31) f4 = 0;
+#pragma unroll
+        for (int d = 1; d < NS; ++d)
+          if ((pat.periods >> d) & 1)
+            r.ovl |= (f0 & __funnelshift_r(f0, f1, 8 * d)) | (f1 & __funnelshift_r(f1, f2, 8 * d)) |
+                     (f2 & __funnelshift_r(f2, f3, 8 * d)) | (f3 & __funnelshift_r(f3, f4, 8 * d));
+        if (lane == 31 && f3 != 0) {
+          for (int j = 4 - (NS - 1); j < 4; ++j) {
+            if (!((f3 >> (8 * j + 7)) & 1)) continue;
+            for (int d = 4 - j; d < NS; ++d) {
+              const long long q2 = (long long)(pos0 + 12 + j + d);
+              if (((pat.periods >> d) & 1) && q2 <= last_q && verify_at(buf, (uint64_t)q2, pat)) r.ovl |= 1;
+            }
+          }
+        }
+      }
       if (EMIT && (f0 | f1 | f2 | f3)) {
         const uint32_t m16 = nibble16(f0) | (nibble16(f1) << 4) | (nibble16(f2) << 8) | (nibble16(f3) << 12);
         r.mask[u >> 1] |= m16 << (16 * (u & 1));
@@ -159,7 +185,10 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
       const uint32_t z1 = (w1 ^ pat.rep[0]) | (w2 ^ pat.rep[1]);
       const uint32_t z2 = (w2 ^ pat.rep[0]) | (w3 ^ pat.rep[1]);
       const uint32_t z3 = (w3 ^ pat.rep[0]) | (w4 ^ pat.rep[1]);
-      const uint32_t any = (haszero_filter(z0) | haszero_filter(z1) | haszero_filter(z2) | haszero_filter(z3)) & k80;
+      // (z - 0x01010101) & ~z per word, the subtraction as IMAD (see add_on_fma_pipe)
+      const uint32_t c_fe = pat.c_fe;
+      const uint32_t any = ((add_on_fma_pipe(z0, pat.one, c_fe) & ~z0) | (add_on_fma_pipe(z1, pat.one, c_fe) & ~z1) |
+                            (add_on_fma_pipe(z2, pat.one, c_fe) & ~z2) | (add_on_fma_pipe(z3, pat.one, c_fe) & ~z3)) & k80;
       if (__any_sync(kFull, any != 0)) {
         if (any != 0) {
           const uint32_t e[4] = {zero_lanes(z0), zero_lanes(z1), zero_lanes(z2), zero_lanes(z3)};
@@ -172,7 +201,15 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
               word &= word - 1;
               const int byte = 4 * j + (bit >> 3);
               const long long q = (long long)(pos0 + byte) - (long long)pat.anchor;
-              if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) m16 |= 1u << byte;
+              if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) {
+                m16 |= 1u << byte;
+                if (OVL) {  // occurrences are rare on this path: look for the overlapping partner directly
+                  for (uint64_t pm = pat.periods; pm; pm &= pm - 1) {
+                    const long long q2 = q + (__ffsll((long long)pm) - 1);
+                    if (q2 <= last_q && verify_at(buf, (uint64_t)q2, pat)) r.ovl |= 1;
+                  }
+                }
+              }
             }
           }
           r.cnt += __popc(m16);
@@ -187,7 +224,7 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 // No inter-warp communication at all: each warp owns its granule and writes its own counters.  With
 // MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
 // an occurrence, so pass 2 never touches the corpus again.
-template <int NS, bool NL, bool MASK, bool ICASE>
+template <int NS, bool NL, bool MASK, bool ICASE, bool OVL = false>
 __global__ void __launch_bounds__(kThreads, 3)
 count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
@@ -198,7 +235,8 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   uint32_t ext;
   load_granule(a.buf, a.n, gran_off, lane, v, ext);
   LaneResult r;
-  classify_granule<NS, MASK, NL, ICASE>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
+  classify_granule<NS, MASK, NL, ICASE, OVL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
+  if (OVL && r.ovl != 0) *a.overlap = 1u;
   if (NL) {
     const uint32_t s = warp_sum(r.nonnl) >> 7;
     if (lane == 0) a.nl_granule[g] = kGranuleBytes - s;
@@ -279,7 +317,9 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
 template <int NS, bool ICASE>
 cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
-  if (masks) {
+  if (a.overlap) {  // list-free xs::count of a bordered pattern (no masks, no newline table)
+    count_kernel<NS, false, false, ICASE, true><<<grid, block, 0, s>>>(pat, a);
+  } else if (masks) {
     if (newlines) count_kernel<NS, true, true, ICASE><<<grid, block, 0, s>>>(pat, a);
     else count_kernel<NS, false, true, ICASE><<<grid, block, 0, s>>>(pat, a);
   } else {

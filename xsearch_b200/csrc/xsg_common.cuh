@@ -29,6 +29,13 @@ struct Pattern {
   // one LOP3 ((w ^ c_nl) & c_7f); as literals the compiler spends one instruction per immediate
   uint32_t c_nl, c_7f;
   uint32_t icase;    // ignore case: bytes[] is already lowered, corpus bytes are folded (ASCII A-Z) before every compare
+  // the value 1 as a run-time multiplier: a + c written as mad.lo(a, one, c) is issued as IMAD on the
+  // multiply-add pipe, which idles while the logic ops of the scan saturate the ALU pipe
+  uint32_t one;
+  uint32_t c_fe;     // 0xfefefeff = -0x01010101 (addend of the has-zero-byte filter)
+  // bit d set <=> d is a period of the pattern, 1 <= d < m (a border of length m - d exists): two occurrences can
+  // only overlap at such a distance
+  uint64_t periods;
 };
 
 // ---- scan kernel launch arguments ---------------------------------------------------------
@@ -44,6 +51,7 @@ struct ScanArgs {
   uint64_t* occ;             // raw occurrence list (pass 2)
   uint64_t occ_cap;
   uint64_t occ_add;          // added to every emitted position (direct mode: the global offset base)
+  unsigned int* overlap;     // OVL variant of pass 1: set to 1 when two occurrences overlap anywhere
 };
 
 // launchers implemented in scan_kernel.cu
@@ -76,7 +84,8 @@ struct DevScalars {
   unsigned int unterminated;
   unsigned int bad_bounds;
   unsigned int ticket[4];
-  unsigned int pad[2];
+  unsigned int overlap;  // count_kernel<.., OVL>: some pair of occurrences overlaps (bordered patterns)
+  unsigned int pad[1];
 };
 // small helpers usable from host code
 
@@ -130,6 +139,12 @@ __device__ __forceinline__ uint32_t zero_lanes(uint32_t z) {
 __device__ __forceinline__ uint32_t nonzero_lanes(uint32_t z) {
   uint32_t b = (z & k7F) + k7F;
   return (b | z) & k80;
+}
+// a + c on the multiply-add pipe (IMAD) instead of the ALU pipe (IADD3 / VIADD); one == 1 at run time
+__device__ __forceinline__ uint32_t add_on_fma_pipe(uint32_t a, uint32_t one, uint32_t c) {
+  uint32_t d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(c));
+  return d;
 }
 // word-level "has a zero byte" predicate (non-zero result <=> some lane is zero); lanes above the
 // lowest zero lane may carry false flags, so use it only as a filter (2 instructions)

@@ -59,6 +59,8 @@ int make_pattern(const uint8_t* p_in, uint32_t m, bool icase, Pattern* out) {
   pat.icase = icase ? 1 : 0;
   pat.c_nl = 0x0a0a0a0au;
   pat.c_7f = 0x7f7f7f7fu;
+  pat.one = 1u;
+  pat.c_fe = 0xfefefeffu;
   auto rep = [](uint8_t c) { return 0x01010101u * c; };
   if (m <= 4) {
     pat.nsimd = m;
@@ -86,6 +88,7 @@ int make_pattern(const uint8_t* p_in, uint32_t m, bool icase, Pattern* out) {
       fail[i + 1] = k;
     }
     pat.bordered = fail[m] > 0;
+    for (uint32_t b = fail[m]; b > 0; b = fail[b]) pat.periods |= 1ull << (m - b);
   }
   *out = pat;
   return XSG_OK;
@@ -127,8 +130,9 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   }
   const bool want_match = (kinds & kMatchKinds) != 0, want_line = (kinds & kLineKinds) != 0;
   const bool want_idx = (kinds & XSG_LINE_INDICES) != 0;
-  // xs::count alone with a pattern that cannot overlap itself needs no occurrence list
-  const bool count_only = kinds == XSG_COUNT && !pat.bordered;
+  // xs::count alone needs no occurrence list when no two occurrences overlap: always true for a border-free
+  // pattern; for a bordered one pass 1 checks it on the fly (OVL variant) and the list path below is the fall-back
+  bool list_path = kinds != XSG_COUNT;
   const uint64_t n_tiles = div_up(n, kTileBytes);
   const uint64_t n_gran = n_tiles * kWarps;
   int rc;
@@ -140,7 +144,8 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   a.gran_count = ctx->gran_count.as<uint32_t>();
   DevScalars* ds = ctx->d_scalars;
 
-  if (count_only) {
+  if (!list_path) {
+    a.overlap = pat.bordered ? &ds->overlap : nullptr;
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
     XSG_CUDA(launch_count(pat, a, false, false, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
@@ -152,9 +157,16 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
     const DevScalars& h = *ctx->h_scalars;
-    st->raw += h.occ_total;
-    part->n_match = h.occ_total - h.zone_sub + h.zone_add;
-  } else {
+    if (h.overlap) {  // overlapping occurrences exist: the greedy selection needs the list
+      list_path = true;
+      a.overlap = nullptr;
+      XSG_CUDA(cudaMemsetAsync(ctx->d_scalars, 0, sizeof(DevScalars), s));
+    } else {
+      st->raw += h.occ_total;
+      part->n_match = h.occ_total - h.zone_sub + h.zone_add;
+    }
+  }
+  if (list_path) {
     if ((rc = ctx->gran_prefix.reserve((n_gran + 2) * sizeof(uint64_t)))) return rc;
     if ((rc = ctx->scan_tmp.reserve(2 * (div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
     if (want_idx) {
