@@ -31,6 +31,10 @@ def main():
         ("count m=1 e", b"e", K.COUNT),
         ("count m=2 th", b"th", K.COUNT),
         ("count m=4 that", b"that", K.COUNT),
+        ("count m=4 then", b"then", K.COUNT),
+        ("match_byte_offsets m=4 that", b"that", K.MATCH_BYTE_OFFSETS),
+        ("match_byte_offsets m=1 e", b"e", K.MATCH_BYTE_OFFSETS),
+        ("all kinds m=8", b"Sherlock", K.COUNT | K.COUNT_LINES | K.MATCH_BYTE_OFFSETS | K.LINE_BYTE_OFFSETS | K.LINE_INDICES | K.LINES),
         ("count m=16", b"inspector said t", K.COUNT),
         ("count m=32", b"needle-needle-needle-needle-0032", K.COUNT),
         ("line_byte_offsets+lines m=8", b"Sherlock", K.LINE_BYTE_OFFSETS | K.LINES),

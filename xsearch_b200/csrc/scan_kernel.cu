@@ -270,12 +270,23 @@ __device__ __forceinline__ void load_gran_mask(const ScanArgs& a, uint64_t g, in
   m.base = a.gran_prefix[g];
 }
 
+// Expansion of one hit granule.  Lane L holds the 128 mask bits of bytes [128 L, 128 L + 128) as four words;
+// a warp scan of the per-lane popcounts gives every lane its first slot.
+//  * few hits (the usual sparse search): every lane stores its own positions directly;
+//  * many hits: the lanes first write 16-bit granule-relative positions into a shared-memory stage (cheap,
+//    bank-parallel), then the warp streams the stage out as consecutive u64 -- one fully coalesced 256-byte
+//    store per 32 hits instead of 32 eight-byte stores scattered over as many sectors.
+constexpr uint32_t kStageCap = 2048;   // hits staged per warp (4 KiB); denser granules (>= 1 hit per 2 bytes) go direct
+constexpr uint32_t kStageMin = 16;     // below this many hits staging costs more than it saves
+
 __global__ void __launch_bounds__(kThreads)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  __shared__ uint16_t s_stage[kWarps][kStageCap];
   const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
   const uint64_t n_gran = a.n_tiles * kWarps;
   // one warp per unit of 32 granules: the serial part of a warp is the handful of hit granules of its unit
-  const uint64_t g0 = ((uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5)) * 32;
+  const uint64_t g0 = ((uint64_t)blockIdx.x * kWarps + warp) * 32;
   if (g0 >= n_gran) return;
   const uint64_t gi = g0 + lane;
   const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
@@ -283,6 +294,7 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   // software pipeline: the mask and prefix of the next hit granule are in flight while this one is expanded
   GranMask next{};
   if (todo) load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
+  uint16_t* __restrict__ stage = s_stage[warp];
   while (todo) {
     const int src = __ffs(todo) - 1;
     todo &= todo - 1;
@@ -295,21 +307,42 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
       const uint32_t t = __shfl_up_sync(kFull, inc, o);
       if (lane >= o) inc += t;
     }
-    const unsigned long long slot = cur.base + (inc - cnt);
-    // one capacity check per lane instead of one per store (the list is sized from the exact total;
-    // it only overflows on the estimate-based first attempt of the non-direct path)
-    if (slot + cnt <= a.occ_cap) {
-      uint64_t* __restrict__ out = a.occ + slot;
-      const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes + (uint64_t)lane * 128 - pat.anchor + a.occ_add;
+    const uint32_t total = __shfl_sync(kFull, inc, 31);
+    // one capacity check per granule (the list is sized from the exact total; it only overflows on the
+    // estimate-based first attempt of the non-direct path)
+    if (cur.base + total > a.occ_cap) continue;
+    uint32_t slot = inc - cnt;
+    uint64_t* __restrict__ out = a.occ + cur.base;
+    const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add;
+    if (total < kStageMin || total > kStageCap) {
+      uint64_t* __restrict__ o = out + slot;
+      const uint64_t p = pos0 + (uint32_t)(lane * 128);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         uint32_t w = cur.w[k];
+#pragma unroll 1
+        while (w) {  // a word rarely holds more than two hits: an unrolled loop is all overhead
+          const int b = __ffs(w) - 1;
+          w &= w - 1;
+          *o++ = p + (uint32_t)(32 * k + b);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t w = cur.w[k];
+        const uint32_t pb = (uint32_t)(lane * 128 + 32 * k);
+#pragma unroll 1
         while (w) {
           const int b = __ffs(w) - 1;
           w &= w - 1;
-          *out++ = pos0 + (uint32_t)(32 * k + b);
+          stage[slot++] = (uint16_t)(pb + b);
         }
       }
+      __syncwarp();
+#pragma unroll 1
+      for (uint32_t j = lane; j < total; j += 32) out[j] = pos0 + stage[j];
+      __syncwarp();  // the stage is rewritten for the next hit granule
     }
   }
 }
