@@ -39,7 +39,10 @@ def main():
         ("count m=32", b"needle-needle-needle-needle-0032", K.COUNT),
         ("line_byte_offsets+lines m=8", b"Sherlock", K.LINE_BYTE_OFFSETS | K.LINES),
     ]
+    only = sys.argv[2] if len(sys.argv) > 2 else ""
     for name, pat, kinds in configs:
+        if only and only not in name:
+            continue
         best = None
         for it in range(6):
             res = ctx.scan(corpus, pat, kinds)

@@ -243,43 +243,65 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   }
   const uint32_t wcnt = warp_sum(r.cnt);
   if (lane == 0) a.gran_count[g] = wcnt;
-  if (MASK && wcnt != 0) a.gran_mask[g * 32 + lane] = make_uint4(r.mask[0], r.mask[1], r.mask[2], r.mask[3]);
+  if (MASK && wcnt != 0) {
+    // stored as [row][lane] halfwords (eight 64-byte warp stores): 16 consecutive bytes of that layout are the
+    // mask bits of 128 consecutive corpus bytes, which is what one lane of pass 2 expands
+    uint16_t* __restrict__ mp = reinterpret_cast<uint16_t*>(a.gran_mask + g * 32) + lane;
+#pragma unroll
+    for (int u = 0; u < kRows; ++u) mp[u * 32] = (uint16_t)(r.mask[u >> 1] >> (16 * (u & 1)));
+  }
 }
 
 // ---- pass 2: ordered emission from the stored masks.  The output position of a granule is the
 // exclusive prefix of the granule counts, so there is no inter-CTA dependency.  A warp inspects 32
 // granule counters at a time and expands the masks of the non-empty ones (512 bytes each).
 //
-// Pass 1 stores a mask as [lane][row] halfwords (one 16-byte store per lane).  Here lane L gathers the
-// eight halfwords of row L/4, lanes 8(L%4)..8(L%4)+7: 128 mask bits that cover the CONTIGUOUS byte range
-// [128 L, 128 L + 128) of the granule.  File order is then lane order, one warp scan of the per-lane
-// popcounts yields every slot, and each lane writes its own hits.
+// Pass 1 stores a mask as [row][lane] halfwords.  Here lane L loads bytes [16 L, 16 L + 16) of it: row L/4,
+// lanes 8(L%4)..8(L%4)+7, i.e. the 128 mask bits of the CONTIGUOUS byte range [128 L, 128 L + 128) of the
+// granule.  File order is then lane order, one warp scan of the per-lane popcounts yields every slot.
 struct GranMask {
   uint32_t w[4];
-  unsigned long long base;
 };
 
 __device__ __forceinline__ void load_gran_mask(const ScanArgs& a, uint64_t g, int lane, GranMask& m) {
-  const uint16_t* __restrict__ h =
-      reinterpret_cast<const uint16_t*>(a.gran_mask + g * 32) + (8 * (lane & 3)) * 8 + (lane >> 2);
-  uint32_t t[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) t[j] = __ldg(h + j * 8);  // lane 8(L%4)+j, row L/4
-#pragma unroll
-  for (int k = 0; k < 4; ++k) m.w[k] = t[2 * k] | (t[2 * k + 1] << 16);
-  m.base = a.gran_prefix[g];
+  const uint4 t = __ldg(a.gran_mask + g * 32 + lane);
+  m.w[0] = t.x;
+  m.w[1] = t.y;
+  m.w[2] = t.z;
+  m.w[3] = t.w;
 }
 
-// Expansion of one hit granule.  Lane L holds the 128 mask bits of bytes [128 L, 128 L + 128) as four words;
-// a warp scan of the per-lane popcounts gives every lane its first slot.
-//  * few hits (the usual sparse search): every lane stores its own positions directly;
-//  * many hits: the lanes first write 16-bit granule-relative positions into a shared-memory stage (cheap,
-//    bank-parallel), then the warp streams the stage out as consecutive u64 -- one fully coalesced 256-byte
-//    store per 32 hits instead of 32 eight-byte stores scattered over as many sectors.
-constexpr uint32_t kStageCap = 2048;   // hits staged per warp (4 KiB); denser granules (>= 1 hit per 2 bytes) go direct
+// st.shared.u16 [addr + OFF], val  -- executed only if cond != 0 (a predicated store, no branch)
+template <int OFF>
+__device__ __forceinline__ void sts16_if(uint32_t addr, uint32_t val, uint32_t cond) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p st.shared.u16 [%0+%3], %1;\n\t}"
+      :: "r"(addr), "h"((unsigned short)val), "r"(cond), "n"(OFF) : "memory");
+}
+// positions (base + bit index) of the three lowest set bits of w -> stage entries 0..2 at shared address saddr;
+// returns the bits that are left
+__device__ __forceinline__ uint32_t stage_three(uint32_t w, uint32_t saddr, uint32_t base) {
+  sts16_if<0>(saddr, base + __ffs(w) - 1, w);
+  w &= w - 1;
+  sts16_if<2>(saddr, base + __ffs(w) - 1, w);
+  w &= w - 1;
+  sts16_if<4>(saddr, base + __ffs(w) - 1, w);
+  return w & (w - 1);
+}
+__device__ __forceinline__ void stage_rest(uint32_t w, uint32_t saddr, uint32_t base) {
+  saddr += 6;
+#pragma unroll 1
+  while (w) {
+    sts16_if<0>(saddr, base + __ffs(w) - 1, 1u);
+    w &= w - 1;
+    saddr += 2;
+  }
+}
+
+constexpr uint32_t kStageCap = 1024;   // hits staged per warp (2 KiB); denser granules (>= 1 hit per 4 bytes) go direct
 constexpr uint32_t kStageMin = 16;     // below this many hits staging costs more than it saves
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   __shared__ uint16_t s_stage[kWarps][kStageCap];
   const int lane = threadIdx.x & 31;
@@ -291,14 +313,25 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   const uint64_t gi = g0 + lane;
   const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
   unsigned todo = __ballot_sync(kFull, c != 0);
-  // software pipeline: the mask and prefix of the next hit granule are in flight while this one is expanded
+  if (todo == 0) return;
+  // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below) and
+  // pulls that granule's mask into L2: the masks are then expanded one granule after the other, and a
+  // one-ahead software pipeline only covers an L2 hit, not a DRAM access
+  unsigned long long my_base = 0;
+  if (c != 0) {
+    my_base = a.gran_prefix[gi];
+    const char* mp = reinterpret_cast<const char*>(a.gran_mask + gi * 32);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(mp + 128 * i));
+  }
   GranMask next{};
-  if (todo) load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
+  load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
   uint16_t* __restrict__ stage = s_stage[warp];
   while (todo) {
     const int src = __ffs(todo) - 1;
     todo &= todo - 1;
     const GranMask cur = next;
+    const unsigned long long base = __shfl_sync(kFull, my_base, src);
     if (todo) load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
     const uint32_t cnt = __popc(cur.w[0]) + __popc(cur.w[1]) + __popc(cur.w[2]) + __popc(cur.w[3]);
     uint32_t inc = cnt;  // inclusive warp scan of the per-lane counts
@@ -310,9 +343,9 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
     const uint32_t total = __shfl_sync(kFull, inc, 31);
     // one capacity check per granule (the list is sized from the exact total; it only overflows on the
     // estimate-based first attempt of the non-direct path)
-    if (cur.base + total > a.occ_cap) continue;
+    if (base + total > a.occ_cap) continue;
     uint32_t slot = inc - cnt;
-    uint64_t* __restrict__ out = a.occ + cur.base;
+    uint64_t* __restrict__ out = a.occ + base;
     const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add;
     if (total < kStageMin || total > kStageCap) {
       uint64_t* __restrict__ o = out + slot;
@@ -328,16 +361,23 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
         }
       }
     } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        uint32_t w = cur.w[k];
-        const uint32_t pb = (uint32_t)(lane * 128 + 32 * k);
-#pragma unroll 1
-        while (w) {
-          const int b = __ffs(w) - 1;
-          w &= w - 1;
-          stage[slot++] = (uint16_t)(pb + b);
-        }
+      // a word of a dense text search holds one hit, sometimes two or three: the first three hits of all four
+      // words are taken by straight-line predicated code (twelve independent chains, no branch), the rare
+      // rest by a loop
+      const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(stage) + 2 * slot;
+      const uint32_t s1 = s0 + 2 * __popc(cur.w[0]);
+      const uint32_t s2 = s1 + 2 * __popc(cur.w[1]);
+      const uint32_t s3 = s2 + 2 * __popc(cur.w[2]);
+      const uint32_t pb = (uint32_t)(lane * 128);
+      const uint32_t r0 = stage_three(cur.w[0], s0, pb);
+      const uint32_t r1 = stage_three(cur.w[1], s1, pb + 32);
+      const uint32_t r2 = stage_three(cur.w[2], s2, pb + 64);
+      const uint32_t r3 = stage_three(cur.w[3], s3, pb + 96);
+      if (__any_sync(kFull, (r0 | r1 | r2 | r3) != 0)) {
+        stage_rest(r0, s0, pb);
+        stage_rest(r1, s1, pb + 32);
+        stage_rest(r2, s2, pb + 64);
+        stage_rest(r3, s3, pb + 96);
       }
       __syncwarp();
 #pragma unroll 1
