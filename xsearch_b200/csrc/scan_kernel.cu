@@ -93,7 +93,7 @@ __device__ __forceinline__ void load_granule(const uint8_t* __restrict__ buf, ui
 }
 
 // Phase 1 for one warp granule: classify, (verify), count.  NS: 1..4 = exact compare of m = NS
-// consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification.
+// consecutive bytes; 5 = filter on pattern bytes (a, a+4) + verification; 6 = 5 + register pre-check.
 // OVL (bordered patterns, xs::count without a list): additionally report whether ANY two occurrences overlap.
 // Two occurrences q < q' overlap only at a distance q' - q that is a period of the pattern (pat.periods).
 template <int NS, bool EMIT, bool NL, bool ICASE, bool OVL>
@@ -191,14 +191,20 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
                             (add_on_fma_pipe(z2, pat.one, c_fe) & ~z2) | (add_on_fma_pipe(z3, pat.one, c_fe) & ~z3)) & k80;
       if (__any_sync(kFull, any != 0)) {
         if (any != 0) {
-          const uint32_t e[4] = {zero_lanes(z0), zero_lanes(z1), zero_lanes(z2), zero_lanes(z3)};
+          const uint32_t zj[4] = {z0, z1, z2, z3};
+          const uint32_t wj[5] = {w0, w1, w2, w3, w4};
           uint32_t m16 = 0;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            uint32_t word = e[j];
+            uint32_t word = zero_lanes(zj[j]);
             while (word) {
               const int bit = __ffs(word) - 1;  // 7, 15, 23 or 31
               word &= word - 1;
+              // NS == 6: the two filter bytes matched; the four bytes from the first one on are still in
+              // registers, so almost every false candidate dies here without touching memory.  (Keeping the
+              // text words alive costs the streaming path registers, hence a variant of its own, chosen by
+              // the host when the filter bytes are frequent ones: Pattern::precheck.)
+              if (NS == 6 && __funnelshift_r(wj[j], wj[j + 1], bit - 7) != pat.word_a) continue;
               const int byte = 4 * j + (bit >> 3);
               const long long q = (long long)(pos0 + byte) - (long long)pat.anchor;
               if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) {
@@ -225,7 +231,7 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 // MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
 // an occurrence, so pass 2 never touches the corpus again.
 template <int NS, bool NL, bool MASK, bool ICASE, bool OVL = false>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, (NS == 6 || OVL) ? 4 : 3)
 count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -409,7 +415,9 @@ cudaError_t launch_count_ic(const Pattern& pat, const ScanArgs& a, bool newlines
     case 2: return launch_count_ns<2, ICASE>(pat, a, newlines, masks, s);
     case 3: return launch_count_ns<3, ICASE>(pat, a, newlines, masks, s);
     case 4: return launch_count_ns<4, ICASE>(pat, a, newlines, masks, s);
-    default: return launch_count_ns<5, ICASE>(pat, a, newlines, masks, s);
+    default:
+      return pat.precheck ? launch_count_ns<6, ICASE>(pat, a, newlines, masks, s)
+                          : launch_count_ns<5, ICASE>(pat, a, newlines, masks, s);
   }
 }
 

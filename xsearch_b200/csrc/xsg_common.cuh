@@ -36,6 +36,8 @@ struct Pattern {
   // bit d set <=> d is a period of the pattern, 1 <= d < m (a border of length m - d exists): two occurrences can
   // only overlap at such a distance
   uint64_t periods;
+  uint32_t word_a;   // m >= 5: pattern bytes [anchor, anchor + 4) as a little-endian word (register pre-check of a candidate)
+  uint32_t precheck; // m >= 5: the chosen filter bytes are frequent ones -> use the variant that pre-checks candidates in registers
 };
 
 // ---- scan kernel launch arguments ---------------------------------------------------------
