@@ -245,6 +245,15 @@ __global__ void add_u64_from_table_kernel(uint64_t* v, uint64_t n, const uint64_
     v[i] += delta;
 }
 
+__global__ void __launch_bounds__(256) overlap_check_kernel(const uint64_t* __restrict__ occ, uint64_t k, uint32_t m,
+                                                            unsigned int* flag) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  bool seen = false;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < k; i += stride)
+    seen |= occ[i + 1] - occ[i] < m;
+  if (seen) *flag = 1u;
+}
+
 __global__ void summary_kernel(const DevScalars* __restrict__ d, int mode, int want_lines, unsigned long long* out) {
   out[0] = d->nl_total;
   out[1] = mode == 1 ? d->occ_total - d->zone_sub + d->zone_add : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
@@ -253,6 +262,12 @@ __global__ void summary_kernel(const DevScalars* __restrict__ d, int mode, int w
 }
 
 }  // namespace
+
+void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned int* flag, cudaStream_t s) {
+  if (k < 2 || m < 2) return;
+  const uint64_t want = div_up(k, 256);
+  overlap_check_kernel<<<(unsigned)(want < 148 * 16 ? want : 148 * 16), 256, 0, s>>>(occ, k, m, flag);
+}
 
 void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, cudaStream_t s) {
   summary_kernel<<<1, 1, 0, s>>>(static_cast<const DevScalars*>(dev_scalars), mode, want_lines, summary);

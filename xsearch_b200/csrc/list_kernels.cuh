@@ -28,6 +28,8 @@ void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, 
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
                         uint64_t* out_b, unsigned long long* total_b, uint64_t n, uint64_t* tmp, cudaStream_t s);
 
+// *flag = 1 if two consecutive entries of the sorted occurrence list are closer than m (overlapping occurrences)
+void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned int* flag, cudaStream_t s);
 // selection flags of the non-zone part of every chunk
 void launch_select(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);
 // per-chunk: greedy resolution (bordered) and emulation of the reference's chunk tail; sets sel[]

@@ -196,10 +196,11 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
                              cudaMemcpyDeviceToHost, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[4], s));
-    // direct mode: for xs::match_byte_offsets of a pattern that cannot overlap itself the occurrence list
-    // IS the result unless a chunk tail of the reference drops one (rare) -- so pass 2 writes global
-    // offsets straight into the result vector and the list kernels read it with a bias
-    const bool direct = (kinds & XSG_MATCH_BYTE_OFFSETS) && !pat.bordered;
+    // direct mode: for xs::match_byte_offsets the occurrence list IS the result unless a chunk tail of the
+    // reference drops one (rare) or -- bordered patterns only -- two occurrences overlap somewhere (checked on
+    // the list).  So pass 2 writes global offsets straight into the result vector and the list kernels read
+    // it with a bias; the select + compact fall-back below covers the exceptions.
+    const bool direct = (kinds & XSG_MATCH_BYTE_OFFSETS) != 0;
     uint64_t k = 0;
     uint64_t* occ_list = nullptr;
     if (direct) {
@@ -213,6 +214,10 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       if (k) {
         XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
         st->launches += 1;
+        if (pat.bordered) {
+          launch_overlap_check(occ_list, k, pat.m, &ds->overlap, s);
+          st->launches += 1;
+        }
       }
     } else {
       uint64_t cap = occ_cap_opt ? occ_cap_opt : std::max<uint64_t>(1u << 20, n / 40);
@@ -247,7 +252,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         if (fam == 0 && direct) {  // only count what the reference's chunk tails would not report
           ListArgs ld = l;
           ld.sel = nullptr;
-          launch_zone(ld, pat, mode, s);
+          launch_zone(ld, pat, kSelMatch, s);  // bordered: meaningful only if nothing overlaps (else fall-back)
           st->launches += pat.m > 1 ? 1 : 0;
           continue;
         }
@@ -298,12 +303,14 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     st->launches += 1;
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
-    if (direct && k > 0 && ctx->h_scalars->drops) {
-      // a chunk tail of the reference skipped occurrences: select + compact the list into a new vector
+    if (direct && k > 0 && (ctx->h_scalars->drops || ctx->h_scalars->overlap)) {
+      // a chunk tail of the reference skipped occurrences, or occurrences overlap (greedy selection needed):
+      // select + compact the list into a new vector
+      const int fb_mode = pat.bordered ? kSelMatchBordered : kSelMatch;
       ListArgs l{buf, n, d_bounds, nb, occ_list, k, ctx->sel.as<uint8_t>(), ctx->gran_prefix.as<uint64_t>(), n_gran,
                  goff, &ds->drops};
-      launch_select(l, pat, kSelMatch, s);
-      launch_zone(l, pat, kSelMatch, s);
+      launch_select(l, pat, fb_mode, s);
+      launch_zone(l, pat, fb_mode, s);
       CompactArgs c{};
       c.l = l;
       c.goff = goff;
