@@ -160,11 +160,12 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
         // lane 31 that is another row or granule, so its last word is checked byte-wise instead.
         uint32_t f4 = __shfl_sync(kFull, f0, (lane + 1) & 31);
         if (lane == 31) f4 = 0;
-#pragma unroll
-        for (int d = 1; d < NS; ++d)
-          if ((pat.periods >> d) & 1)
-            r.ovl |= (f0 & __funnelshift_r(f0, f1, 8 * d)) | (f1 & __funnelshift_r(f1, f2, 8 * d)) |
-                     (f2 & __funnelshift_r(f2, f3, 8 * d)) | (f3 & __funnelshift_r(f3, f4, 8 * d));
+        // For m <= 4 every period is a multiple of the smallest one p, and occurrences at q and q + kp imply
+        // one at q + p: testing the distance p alone is enough (shift = 8p bits, a run-time uniform value,
+        // so the row stays branch-free).
+        const uint32_t sh = pat.ovl_shift;
+        r.ovl |= (f0 & __funnelshift_r(f0, f1, sh)) | (f1 & __funnelshift_r(f1, f2, sh)) |
+                 (f2 & __funnelshift_r(f2, f3, sh)) | (f3 & __funnelshift_r(f3, f4, sh));
         if (lane == 31 && f3 != 0) {
           for (int j = 4 - (NS - 1); j < 4; ++j) {
             if (!((f3 >> (8 * j + 7)) & 1)) continue;

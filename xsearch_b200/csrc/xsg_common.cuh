@@ -37,6 +37,7 @@ struct Pattern {
   // only overlap at such a distance
   uint64_t periods;
   uint32_t word_a;   // m >= 5: pattern bytes [anchor, anchor + 4) as a little-endian word (register pre-check of a candidate)
+  uint32_t ovl_shift; // m <= 4, bordered: 8 x the smallest period (byte-lane shift of the overlap test in pass 1)
   uint32_t precheck; // m >= 5: the chosen filter bytes are frequent ones -> use the variant that pre-checks candidates in registers
 };
 

@@ -93,6 +93,7 @@ int make_pattern(const uint8_t* p_in, uint32_t m, bool icase, Pattern* out) {
     }
     pat.bordered = fail[m] > 0;
     for (uint32_t b = fail[m]; b > 0; b = fail[b]) pat.periods |= 1ull << (m - b);
+    if (pat.bordered) pat.ovl_shift = 8 * (m - fail[m]);  // the longest border gives the smallest period
   }
   *out = pat;
   return XSG_OK;
