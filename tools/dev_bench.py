@@ -38,14 +38,21 @@ def main():
         ("count m=16", b"inspector said t", K.COUNT),
         ("count m=32", b"needle-needle-needle-needle-0032", K.COUNT),
         ("line_byte_offsets+lines m=8", b"Sherlock", K.LINE_BYTE_OFFSETS | K.LINES),
+        ("icase count m=8", b"sherlock", K.COUNT, True),
+        ("icase count_lines+line_indices m=8", b"sherlock", K.COUNT_LINES | K.LINE_INDICES, True),
+        ("icase count m=3 the", b"the", K.COUNT, True),
+        ("icase count m=16", b"inspector said t", K.COUNT, True),
+        ("count m=9 bordered Sherlock S", b"Sherlock S", K.COUNT),
     ]
     only = sys.argv[2] if len(sys.argv) > 2 else ""
-    for name, pat, kinds in configs:
+    for cfg in configs:
+        name, pat, kinds = cfg[:3]
+        icase = len(cfg) > 3 and cfg[3]
         if only and only not in name:
             continue
         best = None
         for it in range(6):
-            res = ctx.scan(corpus, pat, kinds)
+            res = ctx.scan(corpus, pat, kinds, ignore_case=icase)
             t = res.timings()
             cnt = [res.count(k) for k in (K.COUNT, K.COUNT_LINES, K.MATCH_BYTE_OFFSETS, K.LINE_INDICES) if kinds & k]
             raw = res.raw_occurrences

@@ -112,15 +112,13 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 
 #pragma unroll
   for (int u = 0; u < kRows; ++u) {
-    // ignore case: ASCII upper -> lower in registers ('\n' is not touched, so the newline count may use either)
-    const uint32_t w0 = ICASE ? fold_word(v[u].x) : v[u].x, w1 = ICASE ? fold_word(v[u].y) : v[u].y;
-    const uint32_t w2 = ICASE ? fold_word(v[u].z) : v[u].z, w3 = ICASE ? fold_word(v[u].w) : v[u].w;
+    // ignore case costs no folding pass: for a (lowered) pattern byte c that is a letter, tolower(b) == c
+    // <=> (b | 0x20) == c, and for any other c <=> b == c.  The per-byte OR mask (pat.orm[k]: 0x20 in every
+    // lane if pattern byte k is a letter, else 0) rides along in the LOP3 that does the compare.
+    const uint32_t w0 = v[u].x, w1 = v[u].y, w2 = v[u].z, w3 = v[u].w;
     // halo word: lane l takes word 0 of lane l+1; lane 31 takes word 0 of the next row (held by lane 0)
     uint32_t send = w0;
-    if (lane == 0) {
-      send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
-      if (ICASE) send = fold_word(send);
-    }
+    if (lane == 0) send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
     const uint32_t w4 = __shfl_sync(kFull, send, (lane + 1) & 31);
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
@@ -133,13 +131,16 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
     if (NS <= 4) {
-      uint32_t z0 = w0 ^ pat.rep[0], z1 = w1 ^ pat.rep[0], z2 = w2 ^ pat.rep[0], z3 = w3 ^ pat.rep[0];
+      const uint32_t o0 = ICASE ? pat.orm[0] : 0u;
+      uint32_t z0 = (w0 | o0) ^ pat.rep[0], z1 = (w1 | o0) ^ pat.rep[0], z2 = (w2 | o0) ^ pat.rep[0],
+               z3 = (w3 | o0) ^ pat.rep[0];
 #pragma unroll
       for (int k = 1; k < NS; ++k) {  // byte k of the window: data shifted down by k bytes
-        z0 |= __funnelshift_r(w0, w1, 8 * k) ^ pat.rep[k];
-        z1 |= __funnelshift_r(w1, w2, 8 * k) ^ pat.rep[k];
-        z2 |= __funnelshift_r(w2, w3, 8 * k) ^ pat.rep[k];
-        z3 |= __funnelshift_r(w3, w4, 8 * k) ^ pat.rep[k];
+        const uint32_t ok = ICASE ? pat.orm[k] : 0u;
+        z0 |= (__funnelshift_r(w0, w1, 8 * k) | ok) ^ pat.rep[k];
+        z1 |= (__funnelshift_r(w1, w2, 8 * k) | ok) ^ pat.rep[k];
+        z2 |= (__funnelshift_r(w2, w3, 8 * k) | ok) ^ pat.rep[k];
+        z3 |= (__funnelshift_r(w3, w4, 8 * k) | ok) ^ pat.rep[k];
       }
       // exact zero test per byte lane, its addition issued on the multiply-add pipe (see add_on_fma_pipe)
       f0 = ~(add_on_fma_pipe(z0 & k7F, pat.one, pat.c_7f) | z0) & k80;
@@ -182,10 +183,11 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
       }
     } else {
       // filter: pattern byte a at this position AND pattern byte a+4 one word further
-      const uint32_t z0 = (w0 ^ pat.rep[0]) | (w1 ^ pat.rep[1]);
-      const uint32_t z1 = (w1 ^ pat.rep[0]) | (w2 ^ pat.rep[1]);
-      const uint32_t z2 = (w2 ^ pat.rep[0]) | (w3 ^ pat.rep[1]);
-      const uint32_t z3 = (w3 ^ pat.rep[0]) | (w4 ^ pat.rep[1]);
+      const uint32_t o0 = ICASE ? pat.orm[0] : 0u, o1 = ICASE ? pat.orm[1] : 0u;
+      const uint32_t z0 = ((w0 | o0) ^ pat.rep[0]) | ((w1 | o1) ^ pat.rep[1]);
+      const uint32_t z1 = ((w1 | o0) ^ pat.rep[0]) | ((w2 | o1) ^ pat.rep[1]);
+      const uint32_t z2 = ((w2 | o0) ^ pat.rep[0]) | ((w3 | o1) ^ pat.rep[1]);
+      const uint32_t z3 = ((w3 | o0) ^ pat.rep[0]) | ((w4 | o1) ^ pat.rep[1]);
       // (z - 0x01010101) & ~z per word, the subtraction as IMAD (see add_on_fma_pipe)
       const uint32_t c_fe = pat.c_fe;
       const uint32_t any = ((add_on_fma_pipe(z0, pat.one, c_fe) & ~z0) | (add_on_fma_pipe(z1, pat.one, c_fe) & ~z1) |
@@ -205,7 +207,7 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
               // registers, so almost every false candidate dies here without touching memory.  (Keeping the
               // text words alive costs the streaming path registers, hence a variant of its own, chosen by
               // the host when the filter bytes are frequent ones: Pattern::precheck.)
-              if (NS == 6 && __funnelshift_r(wj[j], wj[j + 1], bit - 7) != pat.word_a) continue;
+              if (NS == 6 && (__funnelshift_r(wj[j], wj[j + 1], bit - 7) | (ICASE ? pat.word_or : 0u)) != pat.word_a) continue;
               const int byte = 4 * j + (bit >> 3);
               const long long q = (long long)(pos0 + byte) - (long long)pat.anchor;
               if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) {
@@ -231,12 +233,9 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 // No inter-warp communication at all: each warp owns its granule and writes its own counters.  With
 // MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
 // an occurrence, so pass 2 never touches the corpus again.
-template <int NS, bool NL, bool MASK, bool ICASE, bool OVL = false>
-__global__ void __launch_bounds__(kThreads, (NS == 6 || OVL) ? 4 : 3)
-count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const uint64_t g = (uint64_t)blockIdx.x * kWarps + warp;
+template <int NS, bool NL, bool MASK, bool ICASE, bool OVL>
+__device__ __forceinline__ void count_tile(const Pattern& pat, const ScanArgs& a, uint64_t tile, int lane, int warp) {
+  const uint64_t g = tile * kWarps + warp;
   const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
   uint4 v[kRows];
   uint32_t ext;
@@ -251,11 +250,32 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   const uint32_t wcnt = warp_sum(r.cnt);
   if (lane == 0) a.gran_count[g] = wcnt;
   if (MASK && wcnt != 0) {
-    // stored as [row][lane] halfwords (eight 64-byte warp stores): 16 consecutive bytes of that layout are the
-    // mask bits of 128 consecutive corpus bytes, which is what one lane of pass 2 expands
+    // stored as [row][lane] halfwords (eight 64-byte warp stores): 16 consecutive bytes of that layout are
+    // the mask bits of 128 consecutive corpus bytes, which is what one lane of pass 2 expands
     uint16_t* __restrict__ mp = reinterpret_cast<uint16_t*>(a.gran_mask + g * 32) + lane;
 #pragma unroll
     for (int u = 0; u < kRows; ++u) mp[u * 32] = (uint16_t)(r.mask[u >> 1] >> (16 * (u & 1)));
+  }
+}
+
+template <int NS, bool NL, bool MASK, bool ICASE, bool OVL = false>
+__global__ void __launch_bounds__(kThreads, (NS == 6 || OVL) ? 4 : 3)
+count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  if (!OVL) {  // one tile per CTA
+    count_tile<NS, NL, MASK, ICASE, OVL>(pat, a, blockIdx.x, lane, warp);
+    return;
+  }
+  // OVL variant: a few CTAs per SM stride over the tiles.  Once any CTA has seen overlapping occurrences the
+  // host will redo the search on the list path, so the rest of this pass is wasted work and wasted HBM
+  // traffic: every CTA gives up before its next tile (with a strided grid that really ends the pass; a
+  // tile-per-CTA grid would still have to drain a million empty CTAs).
+  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    unsigned int seen;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.overlap) : "memory");
+    if (seen != 0) return;
+    count_tile<NS, NL, MASK, ICASE, OVL>(pat, a, tile, lane, warp);
   }
 }
 
@@ -398,7 +418,8 @@ template <int NS, bool ICASE>
 cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
   if (a.overlap) {  // list-free xs::count of a bordered pattern (no masks, no newline table)
-    count_kernel<NS, false, false, ICASE, true><<<grid, block, 0, s>>>(pat, a);
+    const dim3 strided((unsigned)(a.n_tiles < 148u * 4 * 4 ? a.n_tiles : 148u * 4 * 4));
+    count_kernel<NS, false, false, ICASE, true><<<strided, block, 0, s>>>(pat, a);
   } else if (masks) {
     if (newlines) count_kernel<NS, true, true, ICASE><<<grid, block, 0, s>>>(pat, a);
     else count_kernel<NS, false, true, ICASE><<<grid, block, 0, s>>>(pat, a);

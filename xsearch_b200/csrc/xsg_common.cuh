@@ -38,6 +38,8 @@ struct Pattern {
   uint64_t periods;
   uint32_t word_a;   // m >= 5: pattern bytes [anchor, anchor + 4) as a little-endian word (register pre-check of a candidate)
   uint32_t ovl_shift; // m <= 4, bordered: 8 x the smallest period (byte-lane shift of the overlap test in pass 1)
+  uint32_t orm[4];   // ignore case: 0x20202020 where SIMD-tested pattern byte k is a letter (see classify_granule), else 0
+  uint32_t word_or;  // ignore case: 0x20 in the lanes of word_a that hold letters
   uint32_t precheck; // m >= 5: the chosen filter bytes are frequent ones -> use the variant that pre-checks candidates in registers
 };
 

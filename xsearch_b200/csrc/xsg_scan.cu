@@ -80,6 +80,16 @@ int make_pattern(const uint8_t* p_in, uint32_t m, bool icase, Pattern* out) {
     pat.rep[1] = rep(p[best + 4]);
     pat.word_a = (uint32_t)p[best] | ((uint32_t)p[best + 1] << 8) | ((uint32_t)p[best + 2] << 16) | ((uint32_t)p[best + 3] << 24);
   }
+  if (icase) {  // the fold is done by OR-ing 0x20 into the text where the (lowered) pattern byte is a letter
+    auto letter = [](uint8_t c) { return c >= 'a' && c <= 'z'; };
+    if (m <= 4) {
+      for (uint32_t i = 0; i < m; ++i) pat.orm[i] = letter(p[i]) ? 0x20202020u : 0u;
+    } else {
+      pat.orm[0] = letter(p[pat.anchor]) ? 0x20202020u : 0u;
+      pat.orm[1] = letter(p[pat.anchor + 4]) ? 0x20202020u : 0u;
+      for (uint32_t i = 0; i < 4; ++i) pat.word_or |= letter(p[pat.anchor + i]) ? 0x20u << (8 * i) : 0u;
+    }
+  }
   // bordered <=> the KMP failure value of the whole pattern is > 0
   uint32_t fail[XSG_MAX_PATTERN + 1];
   fail[0] = 0;
