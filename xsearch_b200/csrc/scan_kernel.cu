@@ -212,12 +212,6 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
               const long long q = (long long)(pos0 + byte) - (long long)pat.anchor;
               if (q >= 0 && q <= last_q && verify_at(buf, (uint64_t)q, pat)) {
                 m16 |= 1u << byte;
-                if (OVL) {  // occurrences are rare on this path: look for the overlapping partner directly
-                  for (uint64_t pm = pat.periods; pm; pm &= pm - 1) {
-                    const long long q2 = q + (__ffsll((long long)pm) - 1);
-                    if (q2 <= last_q && verify_at(buf, (uint64_t)q2, pat)) r.ovl |= 1;
-                  }
-                }
               }
             }
           }
@@ -341,15 +335,19 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
   unsigned todo = __ballot_sync(kFull, c != 0);
   if (todo == 0) return;
-  // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below) and
-  // pulls that granule's mask into L2: the masks are then expanded one granule after the other, and a
-  // one-ahead software pipeline only covers an L2 hit, not a DRAM access
+  // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below).  The
+  // masks are expanded one granule after the other with the next one in flight; to make that next load an L2
+  // hit rather than a DRAM access, the masks of the hit granules four ahead are pulled into L2 (only four:
+  // prefetching a warp's whole unit put 155 MB of masks in flight, more than L2 holds, and DRAM read them twice)
+  const uint32_t lt = (1u << lane) - 1u;
   unsigned long long my_base = 0;
   if (c != 0) {
     my_base = a.gran_prefix[gi];
-    const char* mp = reinterpret_cast<const char*>(a.gran_mask + gi * 32);
+    if (__popc(todo & lt) < 4) {
+      const char* mp = reinterpret_cast<const char*>(a.gran_mask + gi * 32);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(mp + 128 * i));
+      for (int i = 0; i < 4; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(mp + 128 * i));
+    }
   }
   GranMask next{};
   load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
@@ -359,7 +357,14 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
     todo &= todo - 1;
     const GranMask cur = next;
     const unsigned long long base = __shfl_sync(kFull, my_base, src);
-    if (todo) load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
+    if (todo) {
+      load_gran_mask(a, g0 + (__ffs(todo) - 1), lane, next);
+      unsigned t = todo & (todo - 1);
+      t &= t - 1;
+      t &= t - 1;  // the hit granule four behind the current one
+      if (t != 0 && lane < 4)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(a.gran_mask + (g0 + (__ffs(t) - 1)) * 32) + 128 * lane));
+    }
     const uint32_t cnt = __popc(cur.w[0]) + __popc(cur.w[1]) + __popc(cur.w[2]) + __popc(cur.w[3]);
     uint32_t inc = cnt;  // inclusive warp scan of the per-lane counts
 #pragma unroll
@@ -417,9 +422,10 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
 template <int NS, bool ICASE>
 cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
-  if (a.overlap) {  // list-free xs::count of a bordered pattern (no masks, no newline table)
+  if (a.overlap) {  // list-free xs::count of a bordered pattern of <= 4 bytes (no masks, no newline table)
     const dim3 strided((unsigned)(a.n_tiles < 148u * 4 * 4 ? a.n_tiles : 148u * 4 * 4));
-    count_kernel<NS, false, false, ICASE, true><<<strided, block, 0, s>>>(pat, a);
+    if (NS <= 4) count_kernel<(NS <= 4 ? NS : 1), false, false, ICASE, true><<<strided, block, 0, s>>>(pat, a);
+    else return cudaErrorInvalidValue;
   } else if (masks) {
     if (newlines) count_kernel<NS, true, true, ICASE><<<grid, block, 0, s>>>(pat, a);
     else count_kernel<NS, false, true, ICASE><<<grid, block, 0, s>>>(pat, a);

@@ -147,7 +147,9 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   const bool want_idx = (kinds & XSG_LINE_INDICES) != 0;
   // xs::count alone needs no occurrence list when no two occurrences overlap: always true for a border-free
   // pattern; for a bordered one pass 1 checks it on the fly (OVL variant) and the list path below is the fall-back
-  bool list_path = kinds != XSG_COUNT;
+  // (bordered patterns of five bytes and more go straight to the list path: their occurrences are sparse, the
+  // list costs next to nothing, and the filter path has no cheap whole-row overlap test)
+  bool list_path = kinds != XSG_COUNT || (pat.bordered && pat.m > 4);
   const uint64_t n_tiles = div_up(n, kTileBytes);
   const uint64_t n_gran = n_tiles * kWarps;
   int rc;
