@@ -287,6 +287,11 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION on some boxes)
+        # would go there too
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # whatever level is set: not on stdout
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     tags, pat, needle, rate, seed, nbytes = workload_spec(args)
     kinds = 0
