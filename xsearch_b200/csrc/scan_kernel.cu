@@ -33,7 +33,7 @@ __device__ __forceinline__ uint32_t keep_lanes(uint32_t w, long long valid) {
 }
 
 // full compare of the pattern at corpus position q (slow path of the m >= 5 filter)
-__device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t q, const Pattern& pat) {
+__device__ __forceinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t q, const Pattern& pat) {
   if (pat.icase) {
     for (uint32_t k = 0; k < pat.m; ++k)
       if (fold_byte(buf[q + k]) != pat.bytes[k]) return false;
@@ -48,9 +48,10 @@ __device__ __noinline__ bool verify_at(const uint8_t* __restrict__ buf, uint64_t
 // operations: bit 7 of ((w ^ c) & 0x7f) + 0x7f is set iff the low seven bits differ from c; bit 7 of
 // w itself differs from c iff it is set (c = 0x0a has it clear), so the xor is not needed for the
 // final OR.  The four 0x80 flags are summed by one dp4a instead of popc + add.
-__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc, uint32_t c_nl, uint32_t c_7f, uint32_t one) {
+__device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc, uint32_t c_nl, uint32_t c_7f, uint32_t one,
+                                                     uint32_t c_01) {
   const uint32_t b = add_on_fma_pipe((w ^ c_nl) & c_7f, one, c_7f);
-  return __dp4a((b | w) & k80, k01, acc);
+  return __dp4a((b | w) & k80, c_01, acc);
 }
 
 struct LaneResult {
@@ -99,7 +100,7 @@ __device__ __forceinline__ void load_granule(const uint8_t* __restrict__ buf, ui
 template <int NS, bool EMIT, bool NL, bool ICASE, bool OVL>
 __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
                                                  uint64_t gran_off, int lane, const uint4 (&v)[kRows], uint32_t ext,
-                                                 LaneResult& r) {
+                                                 const uint4* __restrict__ konst, LaneResult& r) {
   const uint64_t lane_off = gran_off + (uint64_t)lane * 16;
   const bool partial = gran_off + kGranuleBytes + 16 > n;
 
@@ -109,6 +110,17 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 #pragma unroll
   for (int i = 0; i < kRows / 2; ++i) r.mask[i] = 0;
   const long long last_q = (long long)n - (long long)pat.m;  // last valid occurrence start
+  // The filter variants take their constants from global memory so that they stay in
+  // registers (ScanArgs::konst: saves nine constant-bank reads per row); the exact-compare variants are bound by
+  // the ALU pipe either way and run slightly better with constant-bank operands.
+  constexpr bool kFromGlobal = NS >= 5;
+  const uint4 ka = kFromGlobal ? __ldg(konst) : make_uint4(pat.rep[0], pat.rep[1], pat.rep[2], pat.rep[3]);
+  const uint4 kb = kFromGlobal ? __ldg(konst + 1) : make_uint4(pat.c_nl, pat.c_7f, pat.one, pat.c_fe);
+  const uint4 kc = !ICASE ? make_uint4(0, 0, 0, 0)
+                          : (kFromGlobal ? __ldg(konst + 2) : make_uint4(pat.orm[0], pat.orm[1], pat.orm[2], pat.orm[3]));
+  const uint32_t k_nl = kb.x, k_7f = kb.y, k_one = kb.z, k_fe = kb.w;
+  const uint32_t k_01 = kFromGlobal ? k_one * k01 : k01;
+  const uint32_t k_rep[4] = {ka.x, ka.y, ka.z, ka.w}, k_orm[4] = {kc.x, kc.y, kc.z, kc.w};
 
 #pragma unroll
   for (int u = 0; u < kRows; ++u) {
@@ -123,30 +135,30 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
     if (NL) {  // 128 x (bytes that are not '\n'), accumulated on the multiply-add pipe
-      r.nonnl = not_newline_x128(w0, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
-      r.nonnl = not_newline_x128(w1, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
-      r.nonnl = not_newline_x128(w2, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
-      r.nonnl = not_newline_x128(w3, r.nonnl, pat.c_nl, pat.c_7f, pat.one);
+      r.nonnl = not_newline_x128(w0, r.nonnl, k_nl, k_7f, k_one, k_01);
+      r.nonnl = not_newline_x128(w1, r.nonnl, k_nl, k_7f, k_one, k_01);
+      r.nonnl = not_newline_x128(w2, r.nonnl, k_nl, k_7f, k_one, k_01);
+      r.nonnl = not_newline_x128(w3, r.nonnl, k_nl, k_7f, k_one, k_01);
     }
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
     if (NS <= 4) {
-      const uint32_t o0 = ICASE ? pat.orm[0] : 0u;
-      uint32_t z0 = (w0 | o0) ^ pat.rep[0], z1 = (w1 | o0) ^ pat.rep[0], z2 = (w2 | o0) ^ pat.rep[0],
-               z3 = (w3 | o0) ^ pat.rep[0];
+      const uint32_t o0 = k_orm[0];
+      uint32_t z0 = (w0 | o0) ^ k_rep[0], z1 = (w1 | o0) ^ k_rep[0], z2 = (w2 | o0) ^ k_rep[0],
+               z3 = (w3 | o0) ^ k_rep[0];
 #pragma unroll
       for (int k = 1; k < NS; ++k) {  // byte k of the window: data shifted down by k bytes
-        const uint32_t ok = ICASE ? pat.orm[k] : 0u;
-        z0 |= (__funnelshift_r(w0, w1, 8 * k) | ok) ^ pat.rep[k];
-        z1 |= (__funnelshift_r(w1, w2, 8 * k) | ok) ^ pat.rep[k];
-        z2 |= (__funnelshift_r(w2, w3, 8 * k) | ok) ^ pat.rep[k];
-        z3 |= (__funnelshift_r(w3, w4, 8 * k) | ok) ^ pat.rep[k];
+        const uint32_t ok = k_orm[k];
+        z0 |= (__funnelshift_r(w0, w1, 8 * k) | ok) ^ k_rep[k];
+        z1 |= (__funnelshift_r(w1, w2, 8 * k) | ok) ^ k_rep[k];
+        z2 |= (__funnelshift_r(w2, w3, 8 * k) | ok) ^ k_rep[k];
+        z3 |= (__funnelshift_r(w3, w4, 8 * k) | ok) ^ k_rep[k];
       }
       // exact zero test per byte lane, its addition issued on the multiply-add pipe (see add_on_fma_pipe)
-      f0 = ~(add_on_fma_pipe(z0 & k7F, pat.one, pat.c_7f) | z0) & k80;
-      f1 = ~(add_on_fma_pipe(z1 & k7F, pat.one, pat.c_7f) | z1) & k80;
-      f2 = ~(add_on_fma_pipe(z2 & k7F, pat.one, pat.c_7f) | z2) & k80;
-      f3 = ~(add_on_fma_pipe(z3 & k7F, pat.one, pat.c_7f) | z3) & k80;
+      f0 = ~(add_on_fma_pipe(z0 & k_7f, k_one, k_7f) | z0) & k80;
+      f1 = ~(add_on_fma_pipe(z1 & k_7f, k_one, k_7f) | z1) & k80;
+      f2 = ~(add_on_fma_pipe(z2 & k_7f, k_one, k_7f) | z2) & k80;
+      f3 = ~(add_on_fma_pipe(z3 & k_7f, k_one, k_7f) | z3) & k80;
       if (partial) {  // zero padding / bytes behind n must not match
         const long long lim = last_q + 1 - (long long)pos0;
         f0 = keep_lanes(f0, lim);
@@ -183,15 +195,15 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
       }
     } else {
       // filter: pattern byte a at this position AND pattern byte a+4 one word further
-      const uint32_t o0 = ICASE ? pat.orm[0] : 0u, o1 = ICASE ? pat.orm[1] : 0u;
-      const uint32_t z0 = ((w0 | o0) ^ pat.rep[0]) | ((w1 | o1) ^ pat.rep[1]);
-      const uint32_t z1 = ((w1 | o0) ^ pat.rep[0]) | ((w2 | o1) ^ pat.rep[1]);
-      const uint32_t z2 = ((w2 | o0) ^ pat.rep[0]) | ((w3 | o1) ^ pat.rep[1]);
-      const uint32_t z3 = ((w3 | o0) ^ pat.rep[0]) | ((w4 | o1) ^ pat.rep[1]);
+      const uint32_t o0 = k_orm[0], o1 = k_orm[1];
+      const uint32_t z0 = ((w0 | o0) ^ k_rep[0]) | ((w1 | o1) ^ k_rep[1]);
+      const uint32_t z1 = ((w1 | o0) ^ k_rep[0]) | ((w2 | o1) ^ k_rep[1]);
+      const uint32_t z2 = ((w2 | o0) ^ k_rep[0]) | ((w3 | o1) ^ k_rep[1]);
+      const uint32_t z3 = ((w3 | o0) ^ k_rep[0]) | ((w4 | o1) ^ k_rep[1]);
       // (z - 0x01010101) & ~z per word, the subtraction as IMAD (see add_on_fma_pipe)
-      const uint32_t c_fe = pat.c_fe;
-      const uint32_t any = ((add_on_fma_pipe(z0, pat.one, c_fe) & ~z0) | (add_on_fma_pipe(z1, pat.one, c_fe) & ~z1) |
-                            (add_on_fma_pipe(z2, pat.one, c_fe) & ~z2) | (add_on_fma_pipe(z3, pat.one, c_fe) & ~z3)) & k80;
+      const uint32_t c_fe = k_fe;
+      const uint32_t any = ((add_on_fma_pipe(z0, k_one, c_fe) & ~z0) | (add_on_fma_pipe(z1, k_one, c_fe) & ~z1) |
+                            (add_on_fma_pipe(z2, k_one, c_fe) & ~z2) | (add_on_fma_pipe(z3, k_one, c_fe) & ~z3)) & k80;
       if (__any_sync(kFull, any != 0)) {
         if (any != 0) {
           const uint32_t zj[4] = {z0, z1, z2, z3};
@@ -235,7 +247,7 @@ __device__ __forceinline__ void count_tile(const Pattern& pat, const ScanArgs& a
   uint32_t ext;
   load_granule(a.buf, a.n, gran_off, lane, v, ext);
   LaneResult r;
-  classify_granule<NS, MASK, NL, ICASE, OVL>(pat, a.buf, a.n, gran_off, lane, v, ext, r);
+  classify_granule<NS, MASK, NL, ICASE, OVL>(pat, a.buf, a.n, gran_off, lane, v, ext, a.konst, r);
   if (OVL && r.ovl != 0) *a.overlap = 1u;
   if (NL) {
     const uint32_t s = warp_sum(r.nonnl) >> 7;

@@ -91,6 +91,8 @@ int xsg_init(int device, xsg_ctx** out) {
   XSG_CUDA(cudaMalloc(&c->d_summary, 4 * sizeof(unsigned long long)));
   XSG_CUDA(cudaMemset(c->d_summary, 0, 4 * sizeof(unsigned long long)));
   XSG_CUDA(cudaHostAlloc(&c->h_scalars, sizeof(DevScalars), cudaHostAllocDefault));
+  XSG_CUDA(cudaMalloc(&c->d_konst, 12 * sizeof(uint32_t)));
+  XSG_CUDA(cudaHostAlloc(&c->h_konst, 12 * sizeof(uint32_t), cudaHostAllocDefault));
   // keep freed result memory in the stream-ordered pool instead of returning it to the driver
   cudaMemPool_t pool;
   if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -118,6 +120,8 @@ void xsg_destroy(xsg_ctx* c) {
   cudaFree(c->d_scalars);
   cudaFree(c->d_summary);
   cudaFreeHost(c->h_scalars);
+  cudaFree(c->d_konst);
+  cudaFreeHost(c->h_konst);
   cudaStreamDestroy(c->own_stream);
   cudaStreamDestroy(c->copy_stream);
   delete c;

@@ -57,6 +57,10 @@ struct ScanArgs {
   uint64_t occ_cap;
   uint64_t occ_add;          // added to every emitted position (direct mode: the global offset base)
   unsigned int* overlap;     // OVL variant of pass 1: set to 1 when two occurrences overlap anywhere
+  // {rep[0..3]}, {c_nl, c_7f, one, c_fe}, {orm[0..3]} in GLOBAL memory: values loaded from there stay in
+  // registers, whereas ptxas re-reads kernel parameters from the constant bank in every row of the scan (nine
+  // LDC/LDCU per 16-byte load; it sees through shuffles and empty asm, so a real load it is)
+  const uint4* konst;
 };
 
 // launchers implemented in scan_kernel.cu

@@ -45,6 +45,8 @@ struct xsg_ctx {
   xsg::DevScalars* d_scalars = nullptr;
   unsigned long long* d_summary = nullptr;  // {newlines, matches, matching lines, lines} of the last scan
   xsg::DevScalars* h_scalars = nullptr;  // pinned
+  uint32_t* d_konst = nullptr;           // 12 words: the scan kernel's constants in global memory (see ScanArgs::konst)
+  uint32_t* h_konst = nullptr;           // pinned staging of the same
 };
 
 struct xsg_corpus {

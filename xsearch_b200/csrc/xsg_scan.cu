@@ -160,6 +160,13 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   a.n_tiles = n_tiles;
   a.gran_count = ctx->gran_count.as<uint32_t>();
   DevScalars* ds = ctx->d_scalars;
+  {  // the scan kernel's constants, also in global memory (ScanArgs::konst)
+    uint32_t* h = ctx->h_konst;
+    for (int i = 0; i < 4; ++i) h[i] = pat.rep[i], h[8 + i] = pat.orm[i];
+    h[4] = pat.c_nl, h[5] = pat.c_7f, h[6] = pat.one, h[7] = pat.c_fe;
+    XSG_CUDA(cudaMemcpyAsync(ctx->d_konst, h, 12 * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    a.konst = reinterpret_cast<const uint4*>(ctx->d_konst);
+  }
 
   if (!list_path) {
     a.overlap = pat.bordered ? &ds->overlap : nullptr;
