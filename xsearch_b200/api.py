@@ -36,6 +36,34 @@ def synth_host(n_bytes: int, params: SynthParams, first_block: int = 0) -> np.nd
     return out
 
 
+class _PinnedBlock:
+    """Owner of one xsg_host_alloc block (freed when the last array viewing it is gone)."""
+
+    def __init__(self, nbytes: int):
+        p = C.c_void_p()
+        _check(lib.xsg_host_alloc(max(int(nbytes), 1), C.byref(p)))
+        self.addr, self.nbytes = p.value, int(nbytes)
+
+    def __del__(self):
+        try:
+            if self.addr:
+                lib.xsg_host_free(C.c_void_p(self.addr))
+                self.addr = None
+        except Exception:
+            pass
+
+
+def pinned_empty(n: int, dtype=np.uint64) -> np.ndarray:
+    """An uninitialised array in pinned host memory (xsg_host_alloc): the destination to hand to
+    ``Result.vector(kind, out=...)`` when the result vector is large -- the device->host copy is then a
+    single DMA at PCIe speed instead of a staged copy into pageable memory."""
+    dt = np.dtype(dtype)
+    blk = _PinnedBlock(int(n) * dt.itemsize)
+    buf = (C.c_char * max(blk.nbytes, 1)).from_address(blk.addr)
+    buf._xsg_block = blk  # the array's base keeps buf alive, buf keeps the pinned block alive
+    return np.frombuffer(buf, dtype=dt, count=int(n))
+
+
 def chunk_bounds_host(buf: np.ndarray, min_chunk: int = DEFAULT_MIN_CHUNK) -> np.ndarray:
     """v1 chunking rule (>= min_chunk bytes, extended through the next newline) on a host buffer."""
     n = int(buf.size)
@@ -258,12 +286,17 @@ class Result:
     def count(self, kind: int) -> int:
         return int(lib.xsg_result_count(self._h, kind))
 
-    def vector(self, kind: int) -> np.ndarray:
+    def vector(self, kind: int, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """The result vector on the host.  ``out``: a preallocated uint64 array (e.g. ``pinned_empty``) of at
+        least ``count(kind)`` entries; the filled prefix is returned."""
         n = self.count(kind)
-        out = np.empty(n, dtype=np.uint64)
+        if out is None:
+            out = np.empty(n, dtype=np.uint64)
+        elif out.dtype != np.uint64 or out.size < n or not out.flags.c_contiguous:
+            raise ValueError("out must be a contiguous uint64 array of at least %d entries" % n)
         if n:
             _check(lib.xsg_result_copy(self._h, kind, _u64ptr(out), n))
-        return out
+        return out[:n]
 
     def line_spans(self) -> Tuple[np.ndarray, np.ndarray]:
         n = self.count(LINES)
