@@ -149,10 +149,12 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 #pragma unroll
       for (int k = 1; k < NS; ++k) {  // byte k of the window: data shifted down by k bytes
         const uint32_t ok = k_orm[k];
-        z0 |= (__funnelshift_r(w0, w1, 8 * k) | ok) ^ k_rep[k];
-        z1 |= (__funnelshift_r(w1, w2, 8 * k) | ok) ^ k_rep[k];
-        z2 |= (__funnelshift_r(w2, w3, 8 * k) | ok) ^ k_rep[k];
-        z3 |= (__funnelshift_r(w3, w4, 8 * k) | ok) ^ k_rep[k];
+        const uint32_t s0 = __funnelshift_r(w0, w1, 8 * k), s1 = __funnelshift_r(w1, w2, 8 * k);
+        const uint32_t s2 = __funnelshift_r(w2, w3, 8 * k), s3 = __funnelshift_r(w3, w4, 8 * k);
+        z0 |= (s0 | ok) ^ k_rep[k];
+        z1 |= (s1 | ok) ^ k_rep[k];
+        z2 |= (s2 | ok) ^ k_rep[k];
+        z3 |= (s3 | ok) ^ k_rep[k];
       }
       // exact zero test per byte lane, its addition issued on the multiply-add pipe (see add_on_fma_pipe)
       f0 = ~(add_on_fma_pipe(z0 & k_7f, k_one, k_7f) | z0) & k80;
