@@ -380,6 +380,27 @@ def test_full_size_properties_10gb(xs, ctx):
     assert (np.diff(v.astype(np.int64)) >= 3).all()
     for q in v[:: max(1, v.size // 64)]:
         assert corpus.download(int(q), 3).tobytes() == b"the"
+    # bordered 4-byte literal: list-free count (overlap-detecting pass 1) == direct offsets (overlap check on the
+    # list); the line family's list path can only report fewer
+    r = ctx.scan(corpus, b"that", xs.COUNT)
+    c_free, launches = r.count(xs.COUNT), r.timings().kernel_launches
+    r.free()
+    r = ctx.scan(corpus, b"that", xs.MATCH_BYTE_OFFSETS | xs.COUNT_LINES)
+    v, c_lines = r.vector(xs.MATCH_BYTE_OFFSETS), r.count(xs.COUNT_LINES)
+    r.free()
+    assert c_free == v.size > n // 1000 and c_lines <= c_free
+    assert launches == 4 or (np.diff(v.astype(np.int64)) < 7).any()   # list-free unless "thathat" occurs
+    assert (np.diff(v.astype(np.int64)) >= 4).all()
+    # ignore case (the corpus is lower case but for the injected needle "Sherlock")
+    r = ctx.scan(corpus, b"THAT", xs.COUNT, ignore_case=True)
+    assert r.count(xs.COUNT) == c_free
+    r.free()
+    r = ctx.scan(corpus, b"sherlock", xs.COUNT | xs.LINE_INDICES, ignore_case=True)
+    assert r.count(xs.COUNT) == whole["count"] and np.array_equal(r.vector(xs.LINE_INDICES), whole["li"])
+    r.free()
+    r = ctx.scan(corpus, b"sherlock", xs.COUNT)
+    assert r.count(xs.COUNT) == 0
+    r.free()
     corpus.free()
 
 
