@@ -123,9 +123,21 @@ int alloc_out(xsg_ctx* ctx, uint64_t** p, uint64_t entries) {
   return XSG_OK;
 }
 
+// Waits for an event by polling for the first 20 ms (a scan of a device-resident shard takes a few ms, and a
+// blocking wait adds its wake-up latency to every scan), then blocks.
+cudaError_t wait_event(cudaEvent_t ev) {
+  const auto t0 = std::chrono::steady_clock::now();
+  for (;;) {
+    const cudaError_t e = cudaEventQuery(ev);
+    if (e != cudaErrorNotReady) return e;
+    if (std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20)) return cudaEventSynchronize(ev);
+  }
+}
+
 int read_scalars(xsg_ctx* ctx) {
   XSG_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(DevScalars), cudaMemcpyDeviceToHost, ctx->stream));
-  XSG_CUDA(cudaStreamSynchronize(ctx->stream));
+  XSG_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
+  XSG_CUDA(wait_event(ctx->ev[5]));
   return XSG_OK;
 }
 
@@ -224,7 +236,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     uint64_t k = 0;
     uint64_t* occ_list = nullptr;
     if (direct) {
-      XSG_CUDA(cudaEventSynchronize(ctx->ev[4]));
+      XSG_CUDA(wait_event(ctx->ev[4]));
       k = ctx->h_scalars->occ_total;
       if ((rc = alloc_out(ctx, &part->match_off, k))) return rc;
       occ_list = part->match_off;
@@ -247,7 +259,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       a.occ_cap = cap;
       XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));  // the count travels to the host while this runs
       st->launches += 1;
-      XSG_CUDA(cudaEventSynchronize(ctx->ev[4]));
+      XSG_CUDA(wait_event(ctx->ev[4]));
       k = ctx->h_scalars->occ_total;
       if (k > cap) {  // rare: denser than the estimate -> emit again with the exact capacity
         XSG_CUDA(cudaStreamSynchronize(s));
