@@ -168,16 +168,19 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
         f2 = keep_lanes(f2, lim - 8);
         f3 = keep_lanes(f3, lim - 12);
       }
-      r.cnt += __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
-      if (OVL) {
+      const uint32_t c_row = __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
+      r.cnt += c_row;
+      // OVL: an overlapping pair needs two occurrences within m - 1 <= 3 bytes: either both in this lane's 16
+      // bytes, or the first one in its last three bytes.  Rows where no lane qualifies (three out of four for
+      // a word like "that") skip the test altogether.
+      if (OVL && __any_sync(kFull, c_row >= 2 || (f3 & 0x80808000u) != 0)) {
         // occurrence flags sit at bit 7 of their byte lane: the flag of position j + d, shifted down by d lanes,
         // meets the flag of position j.  The word behind this lane's 16 bytes is word 0 of the next lane; for
         // lane 31 that is another row or granule, so its last word is checked byte-wise instead.
         uint32_t f4 = __shfl_sync(kFull, f0, (lane + 1) & 31);
         if (lane == 31) f4 = 0;
         // For m <= 4 every period is a multiple of the smallest one p, and occurrences at q and q + kp imply
-        // one at q + p: testing the distance p alone is enough (shift = 8p bits, a run-time uniform value,
-        // so the row stays branch-free).
+        // one at q + p: testing the distance p alone is enough (shift = 8p bits, a run-time uniform value).
         const uint32_t sh = pat.ovl_shift;
         r.ovl |= (f0 & __funnelshift_r(f0, f1, sh)) | (f1 & __funnelshift_r(f1, f2, sh)) |
                  (f2 & __funnelshift_r(f2, f3, sh)) | (f3 & __funnelshift_r(f3, f4, sh));
@@ -242,12 +245,19 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 // MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
 // an occurrence, so pass 2 never touches the corpus again.
 template <int NS, bool NL, bool MASK, bool ICASE, bool OVL>
-__device__ __forceinline__ void count_tile(const Pattern& pat, const ScanArgs& a, uint64_t tile, int lane, int warp) {
+__device__ __forceinline__ bool count_tile(const Pattern& pat, const ScanArgs& a, uint64_t tile, int lane, int warp) {
   const uint64_t g = tile * kWarps + warp;
   const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
   uint4 v[kRows];
   uint32_t ext;
   load_granule(a.buf, a.n, gran_off, lane, v, ext);
+  if (OVL) {
+    // give up once any CTA has seen an overlap (see count_kernel).  The flag is read behind the granule
+    // loads, so its latency hides under theirs; the loads of this one tile are all an aborted pass wastes.
+    unsigned int seen;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.overlap) : "memory");
+    if (seen != 0) return true;
+  }
   LaneResult r;
   classify_granule<NS, MASK, NL, ICASE, OVL>(pat, a.buf, a.n, gran_off, lane, v, ext, a.konst, r);
   if (OVL && r.ovl != 0) *a.overlap = 1u;
@@ -264,6 +274,7 @@ __device__ __forceinline__ void count_tile(const Pattern& pat, const ScanArgs& a
 #pragma unroll
     for (int u = 0; u < kRows; ++u) mp[u * 32] = (uint16_t)(r.mask[u >> 1] >> (16 * (u & 1)));
   }
+  return false;
 }
 
 template <int NS, bool NL, bool MASK, bool ICASE, bool OVL = false>
@@ -277,14 +288,10 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   }
   // OVL variant: a few CTAs per SM stride over the tiles.  Once any CTA has seen overlapping occurrences the
   // host will redo the search on the list path, so the rest of this pass is wasted work and wasted HBM
-  // traffic: every CTA gives up before its next tile (with a strided grid that really ends the pass; a
+  // traffic: every CTA gives up at its next tile (with a strided grid that really ends the pass; a
   // tile-per-CTA grid would still have to drain a million empty CTAs).
-  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-    unsigned int seen;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.overlap) : "memory");
-    if (seen != 0) return;
-    count_tile<NS, NL, MASK, ICASE, OVL>(pat, a, tile, lane, warp);
-  }
+  for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
+    if (count_tile<NS, NL, MASK, ICASE, OVL>(pat, a, tile, lane, warp)) return;
 }
 
 // ---- pass 2: ordered emission from the stored masks.  The output position of a granule is the
