@@ -69,6 +69,8 @@ def parse_args():
     ap.add_argument("--gb", type=float, default=None, help="override bytes per GPU (in GB; invalidates the config)")
     ap.add_argument("--e2e-steps", type=int, default=None, help="default min(steps, 6)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", choices=["p2p", "nccl"], default="p2p",
+                    help="N > 1: shard summaries over NVLink peer memory (own kernels) or an NCCL all-gather")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-gb", type=float, default=2.0)
     return ap.parse_args()
@@ -349,7 +351,16 @@ def run_ours(args):
             res = ctx.scan(corpus, pat, kinds, offset_base=shard_base)
             finish(res)
             res.free()
-        if world > 1:  # first use of the collective the timed loop relies on
+        ex = None
+        if world > 1 and args.exchange == "p2p":
+            # shard summaries travel as peer stores over NVLink (xsg_exchange, repo:xsearch_b200/csrc/xsg_exchange.cu)
+            ex = xs.Exchange(ctx)
+            for _ in range(2):
+                res = ctx.scan(corpus, pat, kinds, offset_base=shard_base)
+                ex.push()
+                ex.rebase(res)
+                res.free()
+        elif world > 1:  # first use of the collective the timed loop relies on
             warm = torch.zeros((world, 4), dtype=torch.int64, device="cuda")
             xs.sharded_scan_async(ctx, corpus, pat, kinds, shard_base, warm).free()
         sampler = ClockSampler(local)
@@ -359,7 +370,13 @@ def run_ours(args):
         e0.record(stream)
         table = torch.zeros((world, 4), dtype=torch.int64, device="cuda") if world > 1 else None
         for _ in range(args.steps):
-            if world > 1:
+            if ex is not None:
+                # scan + push of the shard summary into every rank's table + fix-up kernel that waits for the
+                # round on the device: no host round trip, no collective call
+                res = ctx.scan(corpus, pat, kinds, offset_base=shard_base)
+                ex.push()
+                ex.rebase(res)
+            elif world > 1:
                 # scan + all-gather of the device-resident shard summaries + on-device line-index fix-up:
                 # the exchange never returns to the host
                 res = xs.sharded_scan_async(ctx, corpus, pat, kinds, shard_base, table)
@@ -367,7 +384,7 @@ def run_ours(args):
                 res = ctx.scan(corpus, pat, kinds, offset_base=shard_base)
                 results = res.count(xs.TAGS[tags[-1]])
             t = res.timings()
-            launches += t.kernel_launches + (1 if world > 1 and rank > 0 and (kinds & xs.LINE_INDICES) else 0)
+            launches += t.kernel_launches + (2 if ex is not None else (1 if world > 1 and rank > 0 and (kinds & xs.LINE_INDICES) else 0))
             main_ms.append(t.main_kernel_ms)
             raw = res.raw_occurrences
             res.free()
@@ -378,7 +395,7 @@ def run_ours(args):
         if world > 1:
             col = {xs.COUNT: 1, xs.MATCH_BYTE_OFFSETS: 1, xs.COUNT_LINES: 2, xs.LINE_BYTE_OFFSETS: 2, xs.LINE_INDICES: 2,
                    xs.LINES: 3}[xs.TAGS[tags[-1]]]
-            results = int(table[:, col].sum().item())
+            results = int(ex.totals()[:, col].sum()) if ex is not None else int(table[:, col].sum().item())
     total_bytes = nbytes * world
     value = total_bytes * args.steps / (ms * 1e-3) / 1e9
     kernel_ms = float(np.mean(main_ms))
@@ -449,7 +466,9 @@ def run_ours(args):
         "config": {"workload": args.workload, "pattern": pat.decode("latin-1"), "tags": list(tags),
                    "bytes_per_gpu": nbytes, "global_results": int(results), "raw_occurrences_per_gpu": int(raw),
                    "reference_chunks_per_gpu": int(bounds.size), "l2": "inputs (10 GB per GPU) far larger than the 126 MB L2",
-                   "parallelism": "shard%d" % world},
+                   "parallelism": "shard%d" % world,
+                   **({"exchange": "nvlink peer stores (xsg_exchange)" if args.exchange == "p2p" else "nccl all-gather"}
+                      if world > 1 else {})},
         "e2e": e2e,
         "gpu_launches": int(launches),
         "clocks": clocks,

@@ -189,6 +189,26 @@ const uint64_t* xsg_scan_summary_device(xsg_ctx* ctx);
 int xsg_result_rebase_from_table(xsg_result* r, const uint64_t* table_dev, uint32_t stride, uint32_t rank);
 void xsg_result_free(xsg_result* r);
 
+/* ---- shard exchange over NVLink peer memory (no counterpart in the single-host reference) ------
+ * One process per GPU.  Every rank creates an exchange, hands its 64-byte handle to all other ranks (any
+ * transport: a process group, MPI, a file) and connects with the handles of all ranks in rank order.  After each
+ * scan, xsg_exchange_push() launches a kernel that writes the scan's summary {newlines, matches, matching lines,
+ * lines} into the table of EVERY rank -- plain stores over NVLink into memory opened with cudaIpcOpenMemHandle,
+ * then a system-scope release of the round number.  xsg_result_rebase_exchanged() launches the fix-up kernel: it
+ * waits (on the device) until all ranks have published this round and adds the newline counts of the lower ranks
+ * to the result's line indices.  No host round trip and no collective-library call is involved; both calls must
+ * be made by every rank once per round, in this order.  xsg_exchange_totals() waits for the round and copies the
+ * gathered table [world][4] to the host.  The same fix-up through an NCCL all-gather: xsg_scan_summary_device +
+ * xsg_result_rebase_from_table. */
+typedef struct xsg_exchange xsg_exchange;
+#define XSG_EXCHANGE_HANDLE_BYTES 64
+int xsg_exchange_create(xsg_ctx* ctx, uint32_t world, uint32_t rank, xsg_exchange** out, void* handle_out);
+int xsg_exchange_connect(xsg_exchange* x, const void* handles /* world x XSG_EXCHANGE_HANDLE_BYTES */);
+int xsg_exchange_push(xsg_exchange* x);
+int xsg_result_rebase_exchanged(xsg_result* r, xsg_exchange* x);
+int xsg_exchange_totals(xsg_exchange* x, uint64_t* table_host /* world x 4 */);
+void xsg_exchange_destroy(xsg_exchange* x);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,3 +148,73 @@ def test_device_side_summary_and_table_rebase():
     res.free()
     corpus.free()
     ctx.close()
+
+
+def _peer_rank_main(rank, world, port, out_dir):
+    """One rank of the NVLink peer-memory exchange: scan the shard, push the summary into every rank's table,
+    fix the line indices up on the device (xsg_exchange_*), three rounds with three patterns."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch
+    import torch.distributed as dist
+    import xsearch_b200 as xs
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        buf, bounds = _corpus()
+        c0, c1 = xs.shard_chunks(bounds, world)[rank]
+        b0 = int(bounds[c0 - 1]) if c0 else 0
+        ctx = xs.Context(rank)
+        corpus = ctx.corpus_from_host(buf[b0:int(bounds[c1 - 1])], bounds=bounds[c0:c1] - np.uint64(b0))
+        ex = xs.Exchange(ctx)
+        out = {}
+        for i, pat in enumerate((b"Sherlock", b"the", b"zzzz-not-there")):
+            if rank == i % world:
+                torch.cuda._sleep(200_000_000)   # one rank is late: the others must wait on the device
+            res = ctx.scan(corpus, pat, xs.MATCH_BYTE_OFFSETS | xs.LINE_INDICES | xs.COUNT_LINES, offset_base=b0)
+            ex.push()
+            ex.rebase(res)
+            out["m%d" % i] = res.vector(xs.MATCH_BYTE_OFFSETS)
+            out["l%d" % i] = res.vector(xs.LINE_INDICES)
+            out["t%d" % i] = ex.totals()
+            res.free()
+        np.savez(os.path.join(out_dir, "peer%d.npz" % rank), **out)
+        ex.close()
+        corpus.free()
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def _check_peer_outputs(out_dir, world):
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    parts = [np.load(os.path.join(out_dir, "peer%d.npz" % r)) for r in range(world)]
+    for i, pat in enumerate((b"Sherlock", b"the", b"zzzz-not-there")):
+        exp_m = oracle.match_byte_offsets(buf, pat, bounds)
+        exp_l = oracle.line_indices(buf, pat, bounds)
+        assert np.array_equal(np.concatenate([p["m%d" % i] for p in parts]), exp_m), pat
+        assert np.array_equal(np.concatenate([p["l%d" % i] for p in parts]), exp_l), pat
+        for p in parts:  # every rank ends up with the same gathered table
+            t = p["t%d" % i]
+            assert t.shape == (world, 4) and int(t[:, 0].sum()) == int((buf == 10).sum())
+            assert int(t[:, 1].sum()) == exp_m.size and int(t[:, 2].sum()) == exp_l.size
+
+
+@pytest.mark.gpu
+def test_peer_exchange_single_rank(tmp_path):
+    """world = 1: the exchange degenerates to a rank writing into its own table (kernels, rounds, parities)."""
+    import torch.multiprocessing as mp
+    mp.spawn(_peer_rank_main, args=(1, _free_port(), str(tmp_path)), nprocs=1, join=True)
+    _check_peer_outputs(str(tmp_path), 1)
+
+
+@pytest.mark.gpu
+def test_peer_exchange_two_gpus(tmp_path):
+    """Two processes, two GPUs: summaries travel as peer stores over NVLink, no collective call per round."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    mp.spawn(_peer_rank_main, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    _check_peer_outputs(str(tmp_path), 2)

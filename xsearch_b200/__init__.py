@@ -51,6 +51,8 @@ EXPORTS = [
     "xsg_result_part_count", "xsg_result_part_copy", "xsg_result_part_copy_line_lengths", "xsg_result_count",
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
     "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_scan_summary_device", "xsg_result_rebase_from_table", "xsg_result_free",
+    "xsg_exchange_create", "xsg_exchange_connect", "xsg_exchange_push", "xsg_result_rebase_exchanged", "xsg_exchange_totals",
+    "xsg_exchange_destroy",
 ]
 
 
@@ -139,6 +141,12 @@ def _load() -> C.CDLL:
         "xsg_scan_summary_device": (vp, [vp]),
         "xsg_result_rebase_from_table": (i32, [vp, vp, u32, u32]),
         "xsg_result_free": (None, [vp]),
+        "xsg_exchange_create": (i32, [vp, u32, u32, C.POINTER(vp), vp]),
+        "xsg_exchange_connect": (i32, [vp, vp]),
+        "xsg_exchange_push": (i32, [vp]),
+        "xsg_result_rebase_exchanged": (i32, [vp, vp]),
+        "xsg_exchange_totals": (i32, [vp, pu64]),
+        "xsg_exchange_destroy": (None, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -155,8 +163,8 @@ def _check(rc: int) -> None:
         raise XsgError(rc, (lib.xsg_last_error() or b"").decode("utf-8", "replace"))
 
 
-from .api import (Context, Corpus, Result, Searcher, Stream, extern_search, synth_host, chunk_bounds_host, pinned_empty,  # noqa: E402
+from .api import (Context, Corpus, Result, Searcher, Stream, Exchange, extern_search, synth_host, chunk_bounds_host, pinned_empty,  # noqa: E402
                   shard_chunks, shard_exchange, sharded_scan, sharded_scan_async)
 
-__all__ = ["Context", "Corpus", "Result", "Searcher", "Stream", "extern_search", "synth_host", "chunk_bounds_host", "pinned_empty",
+__all__ = ["Context", "Corpus", "Result", "Searcher", "Stream", "Exchange", "extern_search", "synth_host", "chunk_bounds_host", "pinned_empty",
            "shard_chunks", "shard_exchange", "sharded_scan", "sharded_scan_async", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]

@@ -456,6 +456,54 @@ def shard_exchange(newlines: int, counts: Sequence[int], group=None) -> Tuple[in
     return int(excl[0]), [int(x) for x in excl[1:]], [int(x) for x in tot[1:]]
 
 
+class Exchange:
+    """The shard exchange of a multi-GPU search over NVLink peer memory (xsg_exchange, include/xsg.h): after a
+    scan, ``push()`` writes the shard summary into every rank's table with one small kernel, ``rebase(result)``
+    launches the fix-up kernel that waits for all ranks on the device and adds the lower shards' newline counts
+    to the line indices.  Only the 64-byte IPC handles travel through torch.distributed, once."""
+
+    def __init__(self, ctx: "Context", group=None):
+        import torch
+        import torch.distributed as dist
+        self.ctx = ctx
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        h = C.c_void_p()
+        mine = (C.c_ubyte * 64)()
+        _check(lib.xsg_exchange_create(ctx._h, self.world, self.rank, C.byref(h), C.cast(mine, C.c_void_p)))
+        self._h = h
+        dev = torch.device("cuda", ctx.device)
+        t = torch.tensor(list(bytes(mine)), dtype=torch.uint8, device=dev)
+        allh = torch.empty(self.world * 64, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allh, t, group=group)
+        raw = bytes(allh.cpu().numpy().tobytes())
+        _check(lib.xsg_exchange_connect(self._h, C.cast(C.create_string_buffer(raw, len(raw)), C.c_void_p)))
+        dist.barrier(group)  # every rank has mapped every table before the first push
+
+    def push(self) -> None:
+        _check(lib.xsg_exchange_push(self._h))
+
+    def rebase(self, res: "Result") -> None:
+        _check(lib.xsg_result_rebase_exchanged(res._h, self._h))
+
+    def totals(self) -> np.ndarray:
+        """[world, 4] = {newlines, matches, matching lines, lines} of every rank for the last round."""
+        out = np.empty(self.world * 4, dtype=np.uint64)
+        _check(lib.xsg_exchange_totals(self._h, _u64ptr(out)))
+        return out.reshape(self.world, 4)
+
+    def close(self) -> None:
+        if self._h:
+            if self.ctx._h:
+                lib.xsg_exchange_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def sharded_scan_async(ctx: "Context", corpus: "Corpus", pattern: bytes, kinds: int, shard_base: int, table,
                        group=None) -> "Result":
     """Like sharded_scan, but the exchange never returns to the host: the scan's device-resident summary is
