@@ -133,70 +133,19 @@ struct Scan2 {
   unsigned long long* total[2];
 };
 
-__global__ void __launch_bounds__(kScanThreads) exscan_sums_kernel(const __grid_constant__ Scan2 a, uint64_t n,
-                                                                   uint64_t* tmp) {
-  const uint32_t* __restrict__ in = a.in[blockIdx.y];
-  const uint64_t base = (uint64_t)blockIdx.x * kScanTile + (uint64_t)threadIdx.x * kScanItems;
-  uint32_t v = 0;
-  if (base + kScanItems <= n) {
-    const uint4 x = *reinterpret_cast<const uint4*>(in + base), y = *reinterpret_cast<const uint4*>(in + base + 4);
-    v = x.x + x.y + x.z + x.w + y.x + y.y + y.z + y.w;
-  } else {
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i)
-      if (base + i < n) v += in[base + i];
-  }
-  uint32_t total;
-  block_exscan(v, &total);
-  if (threadIdx.x == 0) tmp[(uint64_t)blockIdx.y * gridDim.x + blockIdx.x] = total;
-}
-
-// one block per table: exclusive scan of tmp[y * nblk .. (y + 1) * nblk) in place, total -> *total[y]
-__global__ void __launch_bounds__(1024) exscan_top_kernel(const __grid_constant__ Scan2 a, uint64_t* tmp_all,
-                                                          uint64_t nblk) {
-  __shared__ unsigned long long s_w[32];
-  __shared__ unsigned long long s_carry;
-  uint64_t* tmp = tmp_all + (uint64_t)blockIdx.x * nblk;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) s_carry = 0;
-  __syncthreads();
-  for (uint64_t base = 0; base < nblk; base += 1024) {
-    const uint64_t i = base + threadIdx.x;
-    const unsigned long long v = i < nblk ? tmp[i] : 0;
-    unsigned long long inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const unsigned long long t = __shfl_up_sync(kFull, inc, o);
-      if (lane >= o) inc += t;
-    }
-    if (lane == 31) s_w[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      const unsigned long long w = s_w[lane];
-      unsigned long long winc = w;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long t = __shfl_up_sync(kFull, winc, o);
-        if (lane >= o) winc += t;
-      }
-      s_w[lane] = winc - w;
-    }
-    __syncthreads();
-    const unsigned long long carry = s_carry;
-    const unsigned long long ex = carry + s_w[warp] + inc - v;
-    if (i < nblk) tmp[i] = ex;
-    __syncthreads();
-    if (threadIdx.x == 1023) s_carry = ex + v;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) *a.total[blockIdx.x] = s_carry;
-}
-
-__global__ void __launch_bounds__(kScanThreads) exscan_apply_kernel(const __grid_constant__ Scan2 a, uint64_t n,
-                                                                    const uint64_t* __restrict__ tmp) {
+// Single pass (decoupled look-back between the tiles of a table): a tile of 2048 counters is read once, its
+// exclusive prefix over the earlier tiles comes from their descriptors, and the 64-bit prefixes are written.
+__global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_constant__ Scan2 a, uint64_t n, uint64_t nblk,
+                                                              unsigned long long* desc_all, unsigned int* tickets,
+                                                              uint32_t epoch) {
+  __shared__ unsigned int s_tile;
+  __shared__ unsigned long long s_base;
   const uint32_t* __restrict__ in = a.in[blockIdx.y];
   uint64_t* __restrict__ out = a.out[blockIdx.y];
-  const uint64_t base = (uint64_t)blockIdx.x * kScanTile + (uint64_t)threadIdx.x * kScanItems;
+  if (threadIdx.x == 0) s_tile = atomicAdd(&tickets[blockIdx.y], 1u);
+  __syncthreads();
+  const uint64_t tile = s_tile;
+  const uint64_t base = tile * kScanTile + (uint64_t)threadIdx.x * kScanItems;
   uint32_t x[kScanItems];
   uint32_t v = 0;
   const bool full = base + kScanItems <= n;
@@ -210,7 +159,16 @@ __global__ void __launch_bounds__(kScanThreads) exscan_apply_kernel(const __grid
 #pragma unroll
   for (int i = 0; i < kScanItems; ++i) v += x[i];
   uint32_t total;
-  uint64_t run = tmp[(uint64_t)blockIdx.y * gridDim.x + blockIdx.x] + block_exscan(v, &total);
+  const uint32_t local = block_exscan(v, &total);
+  if (threadIdx.x < 32) {
+    const unsigned long long excl = lookback(desc_all + (uint64_t)blockIdx.y * nblk, tile, total, threadIdx.x, epoch);
+    if (threadIdx.x == 0) {
+      s_base = excl;
+      if (tile + 1 == nblk) *a.total[blockIdx.y] = excl + total;
+    }
+  }
+  __syncthreads();
+  uint64_t run = s_base + local;
   if (full) {
     uint64_t r[kScanItems];
 #pragma unroll
@@ -316,16 +274,15 @@ void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, 
 }
 
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
-                        uint64_t* out_b, unsigned long long* total_b, uint64_t n, uint64_t* tmp, cudaStream_t s) {
+                        uint64_t* out_b, unsigned long long* total_b, uint64_t n, unsigned long long* desc,
+                        unsigned int* tickets, uint32_t epoch, cudaStream_t s) {
   if (n == 0) return;
   const uint64_t nblk = div_up(n, kScanTile);
   Scan2 a{};
   a.in[0] = in_a; a.out[0] = out_a; a.total[0] = total_a;
   a.in[1] = in_b; a.out[1] = out_b; a.total[1] = total_b;
   const unsigned tables = in_b ? 2 : 1;
-  exscan_sums_kernel<<<dim3((unsigned)nblk, tables), kScanThreads, 0, s>>>(a, n, tmp);
-  exscan_top_kernel<<<tables, 1024, 0, s>>>(a, tmp, nblk);
-  exscan_apply_kernel<<<dim3((unsigned)nblk, tables), kScanThreads, 0, s>>>(a, n, tmp);
+  exscan_kernel<<<dim3((unsigned)nblk, tables), kScanThreads, 0, s>>>(a, n, nblk, desc, tickets, epoch);
 }
 
 }  // namespace xsg

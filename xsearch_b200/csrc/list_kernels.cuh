@@ -22,11 +22,12 @@ void launch_check_bounds(const uint8_t* buf, uint64_t n, const uint64_t* bounds,
 
 // sum of a u32 array into *out (out must be zero before)
 void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, cudaStream_t s);
-// exclusive scans u32 -> u64 of one or two tables of n entries in the same three launches
-// (out[i] = sum in[0..i), out[n] = *total = sum); in_b may be nullptr; tmp holds 2 * div_up(n, 2048) u64.
-// The tables must be 16-byte aligned.
+// exclusive scans u32 -> u64 of one or two tables of n entries in ONE launch (out[i] = sum in[0..i),
+// out[n] = *total = sum); in_b may be nullptr.  desc holds 2 * div_up(n, 2048) look-back descriptors (tagged
+// with `epoch`, see lookback()), tickets two zeroed counters.  The tables must be 16-byte aligned.
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
-                        uint64_t* out_b, unsigned long long* total_b, uint64_t n, uint64_t* tmp, cudaStream_t s);
+                        uint64_t* out_b, unsigned long long* total_b, uint64_t n, unsigned long long* desc,
+                        unsigned int* tickets, uint32_t epoch, cudaStream_t s);
 
 // *flag = 1 if two consecutive entries of the sorted occurrence list are closer than m (overlapping occurrences)
 void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned int* flag, cudaStream_t s);
@@ -34,6 +35,8 @@ void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned 
 void launch_select(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);
 // per-chunk: greedy resolution (bordered) and emulation of the reference's chunk tail; sets sel[]
 void launch_zone(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);
+// both; one launch where the zone replay does not depend on select's flags.  Returns the number of launches.
+int launch_select_zone(const ListArgs& a, const Pattern& pat, int mode, cudaStream_t s);
 // count-only variant without an occurrence list: adds to sub (true occurrences inside the tail zones)
 // and add (occurrences the reference reports there)
 void launch_zone_count(const uint8_t* buf, uint64_t n, const uint64_t* bounds, uint64_t nb, const Pattern& pat,
@@ -50,7 +53,8 @@ struct CompactArgs {
   uint64_t* out_line_start;    // xs::lines: (start, len)
   uint64_t* out_line_len;
   uint64_t* selq;              // [k] scratch: compacted positions of the selected occurrences (line kinds)
-  unsigned long long* desc;    // [div_up(k, 2048)] zeroed look-back descriptors
+  unsigned long long* desc;    // [div_up(k, 2048)] look-back descriptors (tagged with epoch, see lookback())
+  uint32_t epoch;
   unsigned int* ticket;        // zeroed
   unsigned long long* total;   // number of selected entries
   unsigned int* unterminated;  // set when the last selected line has no '\n' (xs::lines drops it)

@@ -267,7 +267,17 @@ __device__ __forceinline__ bool count_tile(const Pattern& pat, const ScanArgs& a
   }
   const uint32_t wcnt = warp_sum(r.cnt);
   if (lane == 0) a.gran_count[g] = wcnt;
-  if (MASK && wcnt != 0) {
+  if (MASK && wcnt == 1) {
+    // the usual hit granule of a sparse search: its one position goes into a 2-byte table and pass 2 needs no
+    // mask (512 bytes written here and read there for one set bit)
+    if (r.cnt != 0) {
+      uint32_t bit = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (r.mask[j] != 0) bit = 32 * j + __ffs(r.mask[j]) - 1;  // bit 16 u + b: row u, byte b of this lane
+      a.gran_first[g] = (uint16_t)((bit >> 4) * (kGranuleBytes / kRows) + lane * 16 + (bit & 15));
+    }
+  } else if (MASK && wcnt != 0) {
     // stored as [row][lane] halfwords (eight 64-byte warp stores): 16 consecutive bytes of that layout are
     // the mask bits of 128 consecutive corpus bytes, which is what one lane of pass 2 expands
     uint16_t* __restrict__ mp = reinterpret_cast<uint16_t*>(a.gran_mask + g * 32) + lane;
@@ -354,7 +364,11 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   if (g0 >= n_gran) return;
   const uint64_t gi = g0 + lane;
   const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
-  unsigned todo = __ballot_sync(kFull, c != 0);
+  if (c == 1) {  // no mask for a single occurrence: pass 1 left its position in gran_first
+    const unsigned long long slot = a.gran_prefix[gi];
+    if (slot < a.occ_cap) a.occ[slot] = gi * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add + a.gran_first[gi];
+  }
+  unsigned todo = __ballot_sync(kFull, c > 1);
   if (todo == 0) return;
   // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below).  The
   // masks are expanded one granule after the other with the next one in flight; to make that next load an L2
@@ -362,7 +376,7 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   // prefetching a warp's whole unit put 155 MB of masks in flight, more than L2 holds, and DRAM read them twice)
   const uint32_t lt = (1u << lane) - 1u;
   unsigned long long my_base = 0;
-  if (c != 0) {
+  if (c > 1) {
     my_base = a.gran_prefix[gi];
     if (__popc(todo & lt) < 4) {
       const char* mp = reinterpret_cast<const char*>(a.gran_mask + gi * 32);

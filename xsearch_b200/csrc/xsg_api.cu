@@ -109,7 +109,7 @@ void xsg_destroy(xsg_ctx* c) {
   cudaStreamSynchronize(c->stream);
   cudaStreamSynchronize(c->copy_stream);
   Scratch* all[] = {&c->gran_count, &c->gran_prefix, &c->nl_granule, &c->nl_prefix, &c->scan_tmp, &c->occ,
-                    &c->sel, &c->desc2, &c->selq, &c->gran_mask, &c->stage[0], &c->stage[1], &c->seg_bounds, &c->stage_bounds[0],
+                    &c->sel, &c->desc2, &c->selq, &c->gran_mask, &c->gran_first, &c->stage[0], &c->stage[1], &c->seg_bounds, &c->stage_bounds[0],
                     &c->stage_bounds[1]};
   for (Scratch* s : all) s->release();
   for (auto& ev : c->ev) cudaEventDestroy(ev);

@@ -51,6 +51,8 @@ struct ScanArgs {
   uint32_t* gran_count;      // [granules] occurrences owned by each 4 KiB granule (ownership by anchor byte)
   uint32_t* nl_granule;      // [granules] '\n' per granule (newline mode) or nullptr
   uint4* gran_mask;          // [granules x 32] occurrence bitmask (16 bits per lane and row) of every granule
+                             // that holds two or more occurrences
+  uint16_t* gran_first;      // [granules] position in the granule of the occurrence of a granule that holds ONE
                              // with gran_count != 0, written by pass 1 and read by pass 2; nullptr = none
   const uint64_t* gran_prefix;  // [granules] exclusive prefix of gran_count (pass 2)
   uint64_t* occ;             // raw occurrence list (pass 2)
@@ -92,9 +94,8 @@ struct DevScalars {
   unsigned long long drops;
   unsigned int unterminated;
   unsigned int bad_bounds;
-  unsigned int ticket[4];
-  unsigned int overlap;  // count_kernel<.., OVL>: some pair of occurrences overlaps (bordered patterns)
-  unsigned int pad[1];
+  unsigned int ticket[5];  // tile counters: [0], [1] the two prefix-sum tables, [2], [3] compaction (match / line family)
+  unsigned int overlap;    // count_kernel<.., OVL>: some pair of occurrences overlaps (bordered patterns)
 };
 // small helpers usable from host code
 
@@ -172,15 +173,25 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_s
 
 
 // Decoupled look-back (Merrill & Garland): returns the exclusive prefix of `aggregate` over all
-// tiles before `tile`; called by warp 0 only.  desc[] was zeroed before the launch; every
-// predecessor tile is owned by a resident CTA (cooperative persistent grid) => forward progress.
+// tiles before `tile`; called by warp 0 only.  Tiles are handed out by a ticket counter, so every
+// predecessor tile is owned by a CTA that is already running => forward progress.
+//
+// A descriptor is {status:2, epoch:14, value:48}.  It only counts if it carries the epoch of the launch
+// that reads it, so a table needs no clearing between launches: what an earlier launch left behind reads
+// as "not published yet".  (The host clears the tables when the 14-bit epoch wraps and when a table is
+// reallocated; epoch 0 is never used.)
+constexpr unsigned kEpochShift = 48;
+constexpr unsigned kEpochMask = 0x3fffu;
+constexpr unsigned long long kDescValueMask = (1ull << kEpochShift) - 1;
+
 __device__ __forceinline__ unsigned long long lookback(unsigned long long* desc, uint64_t tile,
-                                                       unsigned long long aggregate, int lane) {
+                                                       unsigned long long aggregate, int lane, uint32_t epoch) {
+  const unsigned long long tag = (unsigned long long)epoch << kEpochShift;
   if (tile == 0) {
-    if (lane == 0) st_relaxed_u64(&desc[0], kPrefix | aggregate);
+    if (lane == 0) st_relaxed_u64(&desc[0], kPrefix | tag | aggregate);
     return 0;
   }
-  if (lane == 0) st_relaxed_u64(&desc[tile], kAggregate | aggregate);
+  if (lane == 0) st_relaxed_u64(&desc[tile], kAggregate | tag | aggregate);
   unsigned long long excl = 0;
   long long idx = (long long)tile - 1;
   while (true) {
@@ -188,14 +199,15 @@ __device__ __forceinline__ unsigned long long lookback(unsigned long long* desc,
     unsigned long long d;
     unsigned pm, need;
     do {
-      d = my >= 0 ? ld_relaxed_u64(&desc[my]) : kPrefix;  // virtual tile -1: prefix 0
-      const unsigned st = (unsigned)(d >> kStatusShift);
+      d = my >= 0 ? ld_relaxed_u64(&desc[my]) : (kPrefix | tag);  // virtual tile -1: prefix 0
+      unsigned st = (unsigned)(d >> kStatusShift);
+      if (((unsigned)(d >> kEpochShift) & kEpochMask) != epoch) st = 0;  // left over from an earlier launch
       pm = __ballot_sync(kFull, st == 2);
       const unsigned inv = __ballot_sync(kFull, st == 0);
       // only the tiles between this one and the nearest inclusive prefix have to be published
       need = pm ? (inv & ((1u << (__ffs(pm) - 1)) - 1u)) : inv;
     } while (need);
-    unsigned long long val = d & kValueMask;
+    unsigned long long val = d & kDescValueMask;
     if (pm && lane > __ffs(pm) - 1) val = 0;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(kFull, val, o);
@@ -203,7 +215,7 @@ __device__ __forceinline__ unsigned long long lookback(unsigned long long* desc,
     if (pm) break;
     idx -= 32;
   }
-  if (lane == 0) st_relaxed_u64(&desc[tile], kPrefix | (excl + aggregate));
+  if (lane == 0) st_relaxed_u64(&desc[tile], kPrefix | tag | (excl + aggregate));
   return excl;
 }
 

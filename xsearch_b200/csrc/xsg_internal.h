@@ -37,7 +37,7 @@ struct xsg_ctx {
   cudaStream_t own_stream = nullptr;
   cudaStream_t copy_stream = nullptr;  // H2D of streamed segments
   cudaEvent_t ev[6] = {};
-  xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2, selq, gran_mask;
+  xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2, selq, gran_mask, gran_first;
   xsg::Scratch stage[2];               // streamed segments (double buffer)
   xsg::Scratch seg_bounds;
   xsg::Scratch stage_bounds[2];        // chunk bounds of the streamed segments
@@ -47,6 +47,7 @@ struct xsg_ctx {
   xsg::DevScalars* h_scalars = nullptr;  // pinned
   uint32_t* d_konst = nullptr;           // 12 words: the scan kernel's constants in global memory (see ScanArgs::konst)
   uint32_t* h_konst = nullptr;           // pinned staging of the same
+  uint32_t epoch = 0;                    // tag of the look-back descriptors of the next launch (xsg::lookback)
 };
 
 struct xsg_corpus {

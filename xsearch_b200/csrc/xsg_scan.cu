@@ -134,6 +134,27 @@ cudaError_t wait_event(cudaEvent_t ev) {
   }
 }
 
+// Look-back descriptor tables (scan_tmp, desc2) are never cleared between launches: every launch tags its
+// descriptors with a fresh 14-bit epoch.  Cleared here: a table that has just been (re)allocated, and both
+// tables when the epoch wraps.
+int desc_table(xsg_ctx* ctx, Scratch& t, uint64_t entries, unsigned long long** out) {
+  const void* before = t.p;
+  if (int rc = t.reserve(entries * sizeof(unsigned long long))) return rc;
+  if (t.p != before) XSG_CUDA(cudaMemsetAsync(t.p, 0, t.cap, ctx->stream));
+  *out = t.as<unsigned long long>();
+  return XSG_OK;
+}
+
+int next_epoch(xsg_ctx* ctx, uint32_t* out) {
+  if (++ctx->epoch > kEpochMask) {
+    ctx->epoch = 1;
+    if (ctx->scan_tmp.p) XSG_CUDA(cudaMemsetAsync(ctx->scan_tmp.p, 0, ctx->scan_tmp.cap, ctx->stream));
+    if (ctx->desc2.p) XSG_CUDA(cudaMemsetAsync(ctx->desc2.p, 0, ctx->desc2.cap, ctx->stream));
+  }
+  *out = ctx->epoch;
+  return XSG_OK;
+}
+
 int read_scalars(xsg_ctx* ctx) {
   XSG_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(DevScalars), cudaMemcpyDeviceToHost, ctx->stream));
   XSG_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
@@ -204,7 +225,8 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   }
   if (list_path) {
     if ((rc = ctx->gran_prefix.reserve((n_gran + 2) * sizeof(uint64_t)))) return rc;
-    if ((rc = ctx->scan_tmp.reserve(2 * (div_up(n_gran, 2048) + 1) * sizeof(uint64_t)))) return rc;
+    unsigned long long* scan_desc = nullptr;
+    if ((rc = desc_table(ctx, ctx->scan_tmp, 2 * (div_up(n_gran, 2048) + 1), &scan_desc))) return rc;
     if (want_idx) {
       if ((rc = ctx->nl_granule.reserve(n_gran * sizeof(uint32_t)))) return rc;
       if ((rc = ctx->nl_prefix.reserve((n_gran + 2) * sizeof(uint64_t)))) return rc;
@@ -212,17 +234,21 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     }
     if ((rc = ctx->gran_mask.reserve(n_gran * 32 * sizeof(uint4)))) return rc;
     a.gran_mask = ctx->gran_mask.as<uint4>();
+    if ((rc = ctx->gran_first.reserve(n_gran * sizeof(uint16_t)))) return rc;
+    a.gran_first = ctx->gran_first.as<uint16_t>();
     a.gran_prefix = ctx->gran_prefix.as<uint64_t>();
     // pass 1: every byte once -> granule counters; then their exclusive prefix
     XSG_CUDA(cudaEventRecord(ctx->ev[1], s));
     XSG_CUDA(launch_count(pat, a, want_idx, true, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[2], s));
     // one set of launches scans both tables: granule occurrence counts and granule newline counts
+    uint32_t epoch;
+    if ((rc = next_epoch(ctx, &epoch))) return rc;
     launch_exscan2_u32(a.gran_count, ctx->gran_prefix.as<uint64_t>(), &ds->occ_total, a.nl_granule,
-                       want_idx ? ctx->nl_prefix.as<uint64_t>() : nullptr, &ds->nl_total, n_gran,
-                       ctx->scan_tmp.as<uint64_t>(), s);
+                       want_idx ? ctx->nl_prefix.as<uint64_t>() : nullptr, &ds->nl_total, n_gran, scan_desc,
+                       &ds->ticket[0], epoch, s);
     XSG_CUDA(cudaGetLastError());
-    st->launches += 4;
+    st->launches += 2;
     // pass 2: positions of the occurrences, expanded from the masks of the granules that hold any.
     // The host needs their number (allocation sizes, grids).
     XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
@@ -275,7 +301,8 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     if (k > 0) {
       if ((rc = ctx->sel.reserve(k))) return rc;
       const uint64_t n_ct = div_up(k, 2048);
-      if ((rc = ctx->desc2.reserve(n_ct * sizeof(unsigned long long)))) return rc;
+      unsigned long long* compact_desc = nullptr;
+      if ((rc = desc_table(ctx, ctx->desc2, n_ct, &compact_desc))) return rc;
       ListArgs l{buf, n, d_bounds, nb, occ_list, k, ctx->sel.as<uint8_t>(), ctx->gran_prefix.as<uint64_t>(), n_gran,
                  direct ? goff : 0, &ds->drops};
       for (int fam = 0; fam < 2; ++fam) {
@@ -288,9 +315,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
           st->launches += pat.m > 1 ? 1 : 0;
           continue;
         }
-        launch_select(l, pat, mode, s);
-        launch_zone(l, pat, mode, s);
-        st->launches += 1 + (pat.m > 1 ? 1 : 0);
+        st->launches += launch_select_zone(l, pat, mode, s);
         CompactArgs c{};
         c.l = l;
         c.goff = goff;
@@ -321,11 +346,11 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
             c.selq = ctx->selq.as<uint64_t>();
           }
         }
-        c.desc = ctx->desc2.as<unsigned long long>();
-        c.ticket = &ds->ticket[1 + fam];
+        c.desc = compact_desc;
+        if ((rc = next_epoch(ctx, &c.epoch))) return rc;
+        c.ticket = &ds->ticket[2 + fam];
         c.total = &ds->sel_total[fam];
         c.unterminated = &ds->unterminated;
-        XSG_CUDA(cudaMemsetAsync(c.desc, 0, n_ct * sizeof(unsigned long long), s));
         launch_compact(c, pat, s);
         XSG_CUDA(cudaGetLastError());
         st->launches += c.selq ? 2 : 1;
@@ -349,12 +374,11 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       uint64_t* fixed = nullptr;
       if ((rc = alloc_out(ctx, &fixed, k))) return rc;
       c.out_match = fixed;
-      const uint64_t n_ct = div_up(k, 2048);
-      c.desc = ctx->desc2.as<unsigned long long>();
-      c.ticket = &ds->ticket[1];
+      c.desc = ctx->desc2.as<unsigned long long>();  // sized above (k > 0)
+      if ((rc = next_epoch(ctx, &c.epoch))) return rc;
+      c.ticket = &ds->ticket[2];
       c.total = &ds->sel_total[0];
       c.unterminated = &ds->unterminated;
-      XSG_CUDA(cudaMemsetAsync(c.desc, 0, n_ct * sizeof(unsigned long long), s));
       launch_compact(c, pat, s);
       XSG_CUDA(cudaGetLastError());
       launch_summary(ds, 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, s);
