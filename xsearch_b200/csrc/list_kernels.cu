@@ -3,6 +3,7 @@
 // exact restatement of the reference's per-chunk result semantics (search_wrappers.h:36-50,
 // 111-123,149-154,163-207) including the scalar-tail quirk of simd::strstr
 // (simd_search.cpp:58-78,169-171,203) -- see SURVEY.md 3.3 for the model.
+#include <cstdlib>
 #include <cooperative_groups.h>
 #include <cooperative_groups/reduce.h>
 
@@ -75,6 +76,8 @@ __global__ void check_bounds_kernel(const uint8_t* __restrict__ buf, uint64_t n,
 
 // ---- reductions / scans over the per-tile and per-granule tables -------------------------------
 __global__ void reduce_u32_kernel(const uint32_t* __restrict__ in, uint64_t n, unsigned long long* out) {
+  pdl_wait();
+  pdl_trigger();
   unsigned long long acc = 0;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
     acc += in[i];
@@ -133,31 +136,41 @@ struct Scan2 {
   unsigned long long* total[2];
 };
 
-// Single pass (decoupled look-back between the tiles of a table): a tile of 2048 counters is read once, its
+// Single pass (decoupled look-back between the tiles of a table): a tile of 8192 counters is read once, its
 // exclusive prefix over the earlier tiles comes from their descriptors, and the 64-bit prefixes are written.
+// Large tiles: the tables are small (2.4 M counters for 10 GB), so what this kernel costs is the serial
+// look-back chain, and that is as long as the number of tiles.
+constexpr int kExItems = 32;
+constexpr int kExTile = kScanThreads * kExItems;
+
 __global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_constant__ Scan2 a, uint64_t n, uint64_t nblk,
                                                               unsigned long long* desc_all, unsigned int* tickets,
                                                               uint32_t epoch) {
   __shared__ unsigned int s_tile;
   __shared__ unsigned long long s_base;
+  pdl_wait();
+  pdl_trigger();
   const uint32_t* __restrict__ in = a.in[blockIdx.y];
   uint64_t* __restrict__ out = a.out[blockIdx.y];
   if (threadIdx.x == 0) s_tile = atomicAdd(&tickets[blockIdx.y], 1u);
   __syncthreads();
   const uint64_t tile = s_tile;
-  const uint64_t base = tile * kScanTile + (uint64_t)threadIdx.x * kScanItems;
-  uint32_t x[kScanItems];
+  const uint64_t base = tile * kExTile + (uint64_t)threadIdx.x * kExItems;
+  uint32_t x[kExItems];
   uint32_t v = 0;
-  const bool full = base + kScanItems <= n;
+  const bool full = base + kExItems <= n;
   if (full) {
-    const uint4 p = *reinterpret_cast<const uint4*>(in + base), q = *reinterpret_cast<const uint4*>(in + base + 4);
-    x[0] = p.x; x[1] = p.y; x[2] = p.z; x[3] = p.w; x[4] = q.x; x[5] = q.y; x[6] = q.z; x[7] = q.w;
+#pragma unroll
+    for (int i = 0; i < kExItems / 4; ++i) {
+      const uint4 p = *reinterpret_cast<const uint4*>(in + base + 4 * i);
+      x[4 * i] = p.x; x[4 * i + 1] = p.y; x[4 * i + 2] = p.z; x[4 * i + 3] = p.w;
+    }
   } else {
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) x[i] = base + i < n ? in[base + i] : 0;
+    for (int i = 0; i < kExItems; ++i) x[i] = base + i < n ? in[base + i] : 0;
   }
 #pragma unroll
-  for (int i = 0; i < kScanItems; ++i) v += x[i];
+  for (int i = 0; i < kExItems; ++i) v += x[i];
   uint32_t total;
   const uint32_t local = block_exscan(v, &total);
   if (threadIdx.x < 32) {
@@ -170,19 +183,17 @@ __global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_const
   __syncthreads();
   uint64_t run = s_base + local;
   if (full) {
-    uint64_t r[kScanItems];
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-      r[i] = run;
-      run += x[i];
-    }
     ulonglong2* o = reinterpret_cast<ulonglong2*>(out + base);
 #pragma unroll
-    for (int i = 0; i < kScanItems / 2; ++i) o[i] = make_ulonglong2(r[2 * i], r[2 * i + 1]);
-    if (base + kScanItems == n) out[n] = run;
+    for (int i = 0; i < kExItems / 2; ++i) {
+      const uint64_t r0 = run, r1 = run + x[2 * i];
+      run = r1 + x[2 * i + 1];
+      o[i] = make_ulonglong2(r0, r1);
+    }
+    if (base + kExItems == n) out[n] = run;
   } else {
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
+    for (int i = 0; i < kExItems; ++i) {
       if (base + i < n) out[base + i] = run;
       run += x[i];
     }
@@ -205,6 +216,8 @@ __global__ void add_u64_from_table_kernel(uint64_t* v, uint64_t n, const uint64_
 
 __global__ void __launch_bounds__(256) overlap_check_kernel(const uint64_t* __restrict__ occ, uint64_t k, uint32_t m,
                                                             unsigned int* flag) {
+  pdl_wait();
+  pdl_trigger();
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   bool seen = false;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < k; i += stride)
@@ -213,6 +226,7 @@ __global__ void __launch_bounds__(256) overlap_check_kernel(const uint64_t* __re
 }
 
 __global__ void summary_kernel(const DevScalars* __restrict__ d, int mode, int want_lines, unsigned long long* out) {
+  pdl_wait();
   out[0] = d->nl_total;
   out[1] = mode == 1 ? d->occ_total - d->zone_sub + d->zone_add : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
   out[2] = d->sel_total[1];
@@ -224,11 +238,11 @@ __global__ void summary_kernel(const DevScalars* __restrict__ d, int mode, int w
 void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned int* flag, cudaStream_t s) {
   if (k < 2 || m < 2) return;
   const uint64_t want = div_up(k, 256);
-  overlap_check_kernel<<<(unsigned)(want < 148 * 16 ? want : 148 * 16), 256, 0, s>>>(occ, k, m, flag);
+  launch_dependent(overlap_check_kernel, dim3((unsigned)(want < 148 * 16 ? want : 148 * 16)), dim3(256), s, occ, k, m, flag);
 }
 
 void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, cudaStream_t s) {
-  summary_kernel<<<1, 1, 0, s>>>(static_cast<const DevScalars*>(dev_scalars), mode, want_lines, summary);
+  launch_dependent(summary_kernel, dim3(1), dim3(1), s, static_cast<const DevScalars*>(dev_scalars), mode, want_lines, summary);
 }
 
 void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, uint32_t stride, uint32_t rank,
@@ -270,19 +284,19 @@ void launch_check_bounds(const uint8_t* buf, uint64_t n, const uint64_t* bounds,
 void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, cudaStream_t s) {
   if (n == 0) return;
   const unsigned grid = (unsigned)(div_up(n, 256 * 8) < 1184 ? div_up(n, 256 * 8) : 1184);
-  reduce_u32_kernel<<<grid, 256, 0, s>>>(in, n, out);
+  launch_dependent(reduce_u32_kernel, dim3(grid), dim3(256), s, in, n, out);
 }
 
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
                         uint64_t* out_b, unsigned long long* total_b, uint64_t n, unsigned long long* desc,
                         unsigned int* tickets, uint32_t epoch, cudaStream_t s) {
   if (n == 0) return;
-  const uint64_t nblk = div_up(n, kScanTile);
+  const uint64_t nblk = div_up(n, kExTile);
   Scan2 a{};
   a.in[0] = in_a; a.out[0] = out_a; a.total[0] = total_a;
   a.in[1] = in_b; a.out[1] = out_b; a.total[1] = total_b;
   const unsigned tables = in_b ? 2 : 1;
-  exscan_kernel<<<dim3((unsigned)nblk, tables), kScanThreads, 0, s>>>(a, n, nblk, desc, tickets, epoch);
+  launch_dependent(exscan_kernel, dim3((unsigned)nblk, tables), dim3(kScanThreads), s, a, n, nblk, desc, tickets, epoch);
 }
 
 }  // namespace xsg

@@ -292,6 +292,7 @@ __global__ void __launch_bounds__(kThreads, (NS == 6 || OVL) ? 4 : 3)
 count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
+  pdl_trigger();  // the kernel behind this one (prefix sums / reduction) waits for this grid at its top
   if (!OVL) {  // one tile per CTA
     count_tile<NS, NL, MASK, ICASE, OVL>(pat, a, blockIdx.x, lane, warp);
     return;
@@ -355,6 +356,8 @@ constexpr uint32_t kStageMin = 16;     // below this many hits staging costs mor
 
 __global__ void __launch_bounds__(kThreads, 8)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ uint16_t s_stage[kWarps][kStageCap];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -496,7 +499,7 @@ cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cud
   (void)sm_count;
   const uint64_t units = div_up(a.n_tiles * kWarps, 32);  // units of 32 granules, one warp each
   const dim3 grid((unsigned)div_up(units, kWarps)), block(kThreads);
-  emit_kernel<<<grid, block, 0, s>>>(pat, a);
+  launch_dependent(emit_kernel, grid, block, s, pat, a);
   return cudaGetLastError();
 }
 

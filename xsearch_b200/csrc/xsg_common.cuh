@@ -3,6 +3,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+#include <utility>
+
 #include "../../include/xsg.h"
 
 namespace xsg {
@@ -217,6 +220,36 @@ __device__ __forceinline__ unsigned long long lookback(unsigned long long* desc,
   }
   if (lane == 0) st_relaxed_u64(&desc[tile], kPrefix | tag | (excl + aggregate));
   return excl;
+}
+
+// ---- programmatic dependent launch ----------------------------------------------------------------
+// The kernels of one search form chains on one stream (count -> prefix sums; select -> compact -> format ->
+// summary; count -> reduce -> zone count -> summary), each a few microseconds long, so the launch latency
+// between them is a visible part of the step.  A kernel launched with launch_dependent() may be scheduled
+// while its predecessor is still running: the predecessor says pdl_trigger() at its top ("my CTAs have all
+// started, get the next grid ready"), the dependent says pdl_wait() at ITS top, which returns once the
+// predecessor grid has completed and its writes are visible.  Nothing is read or written before pdl_wait().
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static const bool on = std::getenv("XSG_NO_PDL") == nullptr;
+  return on;
+}
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
 }
 
 #endif  // __CUDACC__

@@ -46,7 +46,8 @@ struct xsg_ctx {
   unsigned long long* d_summary = nullptr;  // {newlines, matches, matching lines, lines} of the last scan
   xsg::DevScalars* h_scalars = nullptr;  // pinned
   uint32_t* d_konst = nullptr;           // 12 words: the scan kernel's constants in global memory (see ScanArgs::konst)
-  uint32_t* h_konst = nullptr;           // pinned staging of the same
+  uint32_t* h_konst = nullptr;           // pinned staging of the same (= what d_konst holds once konst_valid)
+  bool konst_valid = false;
   uint32_t epoch = 0;                    // tag of the look-back descriptors of the next launch (xsg::lookback)
 };
 

@@ -194,10 +194,14 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
   a.gran_count = ctx->gran_count.as<uint32_t>();
   DevScalars* ds = ctx->d_scalars;
   {  // the scan kernel's constants, also in global memory (ScanArgs::konst)
-    uint32_t* h = ctx->h_konst;
-    for (int i = 0; i < 4; ++i) h[i] = pat.rep[i], h[8 + i] = pat.orm[i];
-    h[4] = pat.c_nl, h[5] = pat.c_7f, h[6] = pat.one, h[7] = pat.c_fe;
-    XSG_CUDA(cudaMemcpyAsync(ctx->d_konst, h, 12 * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    uint32_t k[12];
+    for (int i = 0; i < 4; ++i) k[i] = pat.rep[i], k[8 + i] = pat.orm[i];
+    k[4] = pat.c_nl, k[5] = pat.c_7f, k[6] = pat.one, k[7] = pat.c_fe;
+    if (!ctx->konst_valid || std::memcmp(k, ctx->h_konst, sizeof k) != 0) {  // same pattern as last time: already there
+      std::memcpy(ctx->h_konst, k, sizeof k);
+      XSG_CUDA(cudaMemcpyAsync(ctx->d_konst, ctx->h_konst, sizeof k, cudaMemcpyHostToDevice, s));
+      ctx->konst_valid = true;
+    }
     a.konst = reinterpret_cast<const uint4*>(ctx->d_konst);
   }
 
