@@ -152,6 +152,61 @@ def test_pattern_lengths_and_tile_edges(xs, ctx, oracle, m):
         run_case(xs, ctx, oracle, buf, pat, bounds, ("edges", m, n))
 
 
+@pytest.mark.parametrize("m", [1, 3, 4, 8, 21])
+def test_single_hit_granules(xs, ctx, oracle, m):
+    """A granule that holds exactly one occurrence has no mask: its position travels in a 2-byte table
+    (gran_first).  One occurrence per granule, at every kind of place a granule has: first / last byte of a lane's
+    16 bytes, of a row, of the granule, across the granule edge, plus granules with none and with two."""
+    pat = (b"Qwertyuiopasdfghjklzx")[:m]
+    p = np.frombuffer(pat, dtype=np.uint8)
+    gran, row = 4096, 512
+    places = [0, 1, 15, 16, 17, row - m, row - 1, row, row + 15, 31 * 16, 31 * 16 + 15 - (m - 1), 7 * row,
+              7 * row + 31 * 16, gran - m, gran - 1, gran - (m + 1) // 2, 2047, 2048, 3 * row + 255]
+    n = (len(places) + 3) * gran + 100
+    buf = np.full(n, ord("."), dtype=np.uint8)
+    buf[np.arange(61, n, 67)] = ord("\n")
+    for i, off in enumerate(places):
+        pos = (i + 1) * gran + off  # granule 0 and the last ones stay empty or get two occurrences below
+        if pos + m <= n:
+            buf[pos:pos + m] = p
+    last = (len(places) + 1) * gran
+    buf[last + 100:last + 100 + m] = p
+    buf[last + 3000:last + 3000 + m] = p
+    buf[n - 1] = ord("\n")
+    for chunk in (5000, 20000):
+        bounds = gen_cases._chunk_bounds(buf, chunk)
+        run_case(xs, ctx, oracle, buf, pat, bounds, ("single-hit granules", m, chunk))
+
+
+def test_lookback_epoch_wrap(xs, ctx, oracle):
+    """The look-back descriptors of the prefix sums and of the compaction are never cleared between launches:
+    every launch tags them with a 14-bit epoch, and the tables are cleared when it wraps.  Enough list-path
+    searches to wrap it twice, on two corpus sizes (the tables of the larger one keep stale entries while the
+    smaller one runs); every result is checked."""
+    rng = np.random.default_rng(99)
+    cases = []
+    for n in (300_000, 40_000):
+        buf = gen_cases._random_text(rng, n, b"the quick brown fox\n", 0.05)
+        bounds = gen_cases._chunk_bounds(buf, 20000)
+        exp = expected(oracle, buf, b"the", bounds)
+        cases.append((ctx.corpus_from_host(buf, bounds=bounds), exp))
+    kinds = xs.COUNT_LINES | xs.LINE_INDICES | xs.MATCH_BYTE_OFFSETS
+    try:
+        for it in range(17000):  # two tagged launches per search (prefix sums, line compaction): wraps at 8192, 16383
+            # an epoch comes back to the same table 16383 searches later: it % 5 puts the other corpus there
+            corpus, exp = cases[0 if it % 5 < 2 else 1]
+            res = ctx.scan(corpus, b"the", kinds)
+            assert res.count(xs.COUNT_LINES) == exp["count_lines"], it
+            assert res.count(xs.MATCH_BYTE_OFFSETS) == exp["count"], it
+            if it % 97 == 0 or 8150 < it < 8250 or 16340 < it < 16440:
+                assert np.array_equal(res.vector(xs.LINE_INDICES), exp["line_idx"]), it
+                assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp["match"]), it
+            res.free()
+    finally:
+        for corpus, _ in cases:
+            corpus.free()
+
+
 @pytest.mark.parametrize("pat", [b"aba", b"abab", b"aa", b"that", b"abcab", b"abcabcab", b"going-go", b"x" * 9,
                                  b"needle-needle-needle-needle-0032-needle"])
 def test_bordered_count_without_list(xs, ctx, oracle, pat):
