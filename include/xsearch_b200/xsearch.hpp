@@ -17,7 +17,8 @@
 //     count tags yield running totals, the last one is the total                      test/src/xsearchTest.cpp:735-739
 //
 // What runs underneath is NOT the reference's thread pool: max_num_readers reader threads pread the file
-// into pinned segments, one pusher thread hands them to libxsg.so (xsg_stream_push: H2D copy overlapped
+// into pinned segments (all of them 8 MiB slices of the same segment, so segments complete in file order at the
+// speed of all readers together), one pusher thread hands them to libxsg.so (xsg_stream_push: H2D copy overlapped
 // with the scan of the previous segment on the GPU) and publishes the result parts in file order.
 // There is no CPU search path: without a CUDA device extern_search throws.
 #pragma once
@@ -324,35 +325,56 @@ class Searcher {
     _cv.notify_all();
   }
 
-  // ---- reader threads: pread blocks into free pinned buffers, in block order ---------------------------
+  // ---- reader threads: ALL of them pread slices of the SAME block (then the next one) ------------------------
+  // One pread is a kernel memcpy out of the page cache, a few GB/s per thread.  With a block per reader the
+  // first block -- and so the first H2D copy -- is ready only after one thread has copied all of it, and blocks
+  // complete out of order; with slices the blocks complete in order at the speed of all readers together, and
+  // the number of pinned buffers does not grow with the number of readers.
+  static constexpr uint64_t kSliceBytes = 8ull << 20;
+
   void run_reader() {
     for (;;) {
       int buf;
       size_t i;
+      uint64_t lo, hi;
       {
-        // a buffer is taken BEFORE the block index, so block i always owns a buffer before block i + 1
         std::unique_lock lock(_m);
-        _cv.wait(lock, [&] { return !_free.empty() || _failed.load() || _next_block >= _blocks.size(); });
+        _cv.wait(lock, [&] { return _cur_buf >= 0 || !_free.empty() || _failed.load() || _next_block >= _blocks.size(); });
         if (_failed.load() || _next_block >= _blocks.size()) return;
-        buf = _free.back();
-        _free.pop_back();
-        i = _next_block++;
+        if (_cur_buf < 0) {  // open the next block: it gets its buffer before any later block can
+          _cur_buf = _free.back();
+          _free.pop_back();
+          _next_slice = 0;
+          _slices_left[_next_block] = (_blocks[_next_block].len + kSliceBytes - 1) / kSliceBytes;
+        }
+        i = _next_block;
+        buf = _cur_buf;
+        const detail::Block& b = _blocks[i];
+        lo = _next_slice * kSliceBytes;
+        hi = std::min<uint64_t>(b.len, lo + kSliceBytes);
+        if (hi >= b.len) {  // that was its last slice: the next reader opens the next block
+          ++_next_block;
+          _cur_buf = -1;
+        } else {
+          ++_next_slice;
+        }
       }
       const detail::Block& b = _blocks[i];
       uint8_t* dst = _bufs[buf]->p + _headroom;
-      uint64_t done = 0;
-      while (done < b.len) {
-        const ssize_t r = ::pread(_fd, dst + done, static_cast<size_t>(std::min<uint64_t>(b.len - done, 1u << 30)),
-                                  static_cast<off_t>(b.off + done));
+      uint64_t done = lo;
+      while (done < hi) {
+        const ssize_t r = ::pread(_fd, dst + done, static_cast<size_t>(hi - done), static_cast<off_t>(b.off + done));
         if (r <= 0) {
           fail("xs::extern_search: read error (file truncated while searching?)");
           return;
         }
         done += static_cast<uint64_t>(r);
       }
+      bool complete;
       {
         std::unique_lock lock(_m);
-        _ready[i] = buf;
+        complete = --_slices_left[i] == 0;
+        if (complete) _ready[i] = buf;
       }
       _cv.notify_all();
     }
@@ -425,7 +447,8 @@ class Searcher {
   }
 
   void pusher_body() {
-    const size_t nbuf = static_cast<size_t>(_num_readers) + 2;
+    // one block being read (two around a block edge), one being copied to the device, one whose results are collected
+    const size_t nbuf = 4;
     for (size_t i = 0; i < nbuf && i < _blocks.size() + 1 && !_blocks.empty(); ++i) {
       auto b = std::make_unique<detail::Pinned>();
       if (!b->alloc(static_cast<size_t>(_headroom + _max_block + 64))) throw std::runtime_error(detail::last_error("pinned buffer"));
@@ -433,6 +456,7 @@ class Searcher {
       _free.push_back(static_cast<int>(i));
     }
     _ready.assign(_blocks.size(), -1);
+    _slices_left.assign(_blocks.size(), 0);
     for (int t = 0; t < _num_readers; ++t) _readers.emplace_back(&Searcher::run_reader, this);
 
     Inflight prev;          // pushed, results not collected yet
@@ -542,12 +566,15 @@ class Searcher {
   xsg_stream* _stream = nullptr;
   xsg_timings _timings{};
 
-  mutable std::mutex _m;  // guards _free, _ready, _next_block, _error
+  mutable std::mutex _m;  // guards _free, _ready, _next_block, _next_slice, _cur_buf, _slices_left, _error
   std::condition_variable _cv;
   std::vector<std::unique_ptr<detail::Pinned>> _bufs;
   std::vector<int> _free;
   std::vector<int> _ready;
-  size_t _next_block = 0;
+  size_t _next_block = 0;           // block whose slices are being handed out
+  uint64_t _next_slice = 0;         // next slice of it
+  int _cur_buf = -1;                // its buffer (-1: not opened yet)
+  std::vector<uint64_t> _slices_left;
   std::string _error;
   std::atomic<bool> _failed{false};
 

@@ -18,8 +18,8 @@ EOF
 ls -l $F > $O
 echo "host cores: $(nproc)" >> $O
 : > $O.err
-for tag in count line_indices lines; do
-  for r in 1 2 4 8 16; do
+for tag in count lines; do
+  for r in 1 4 8 12; do
     for rep in 1 2; do
       s=$(date +%s.%N)
       n=$(./xsearch_b200/cpp/xsgrep --tag $tag --readers $r Sherlock $F 2>> $O.err | wc -l)
