@@ -72,6 +72,8 @@ def parse_args():
     ap.add_argument("--exchange", choices=["p2p", "nccl"], default="p2p",
                     help="N > 1: shard summaries over NVLink peer memory (own kernels) or an NCCL all-gather")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--clock-interval-ms", type=float, default=10.0,
+                    help="pause between two NVML clock samples during the timed region")
     ap.add_argument("--cpu-sample-gb", type=float, default=2.0)
     return ap.parse_args()
 
@@ -108,9 +110,10 @@ def workload_spec(args):
 class ClockSampler(threading.Thread):
     """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, interval_ms: float = 10.0):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self.interval = max(0.001, interval_ms * 1e-3)
         self._stop_evt = threading.Event()
         self.ok = False
         try:
@@ -146,7 +149,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.002)
+            self._stop_evt.wait(self.interval)
 
     def stop(self):
         self._stop_evt.set()
@@ -363,7 +366,7 @@ def run_ours(args):
         elif world > 1:  # first use of the collective the timed loop relies on
             warm = torch.zeros((world, 4), dtype=torch.int64, device="cuda")
             xs.sharded_scan_async(ctx, corpus, pat, kinds, shard_base, warm).free()
-        sampler = ClockSampler(local)
+        sampler = ClockSampler(local, args.clock_interval_ms)
         barrier()
         sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
