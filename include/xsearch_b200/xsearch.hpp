@@ -21,6 +21,10 @@
 // speed of all readers together), one pusher thread hands them to libxsg.so (xsg_stream_push: H2D copy overlapped
 // with the scan of the previous segment on the GPU) and publishes the result parts in file order.
 // There is no CPU search path: without a CUDA device extern_search throws.
+//
+// Regular expressions (the reference sends a pattern to re2 when utils.h:17-24 says it is one): the GPU scans for
+// the literals every match must contain, the host runs the expression over the candidate lines only
+// (regex_prefilter.hpp).  Options::pattern_mode forces either reading of the pattern.
 #pragma once
 
 #include <fcntl.h>
@@ -43,6 +47,7 @@
 
 #include "../xsg.h"
 #include "metafile.hpp"
+#include "regex_prefilter.hpp"
 
 namespace xs {
 
@@ -85,6 +90,9 @@ struct Options {
   uint64_t min_chunk = XSG_DEFAULT_MIN_CHUNK;   // v1: chunks of >= 16 MiB, extended through the next '\n'
   uint64_t segment_bytes = 256ull << 20;        // bytes read / copied / scanned per pipeline step
   bool ignore_case = false;                     // set by the ignore_case overloads of extern_search
+  // AUTO = the reference's rule (xs::use_str_as_regex, utils.h:17-24); LITERAL / REGEX force one reading
+  enum class PatternMode { AUTO, LITERAL, REGEX };
+  PatternMode pattern_mode = PatternMode::AUTO;
 };
 
 // ---- result collector ------------------------------------------------------------------------------
@@ -218,8 +226,21 @@ class Searcher {
   Searcher(std::string pattern, const std::string& file_path, const std::string& meta_file_path, int num_threads,
            int max_num_readers, Options opt = {})
       : _pattern(std::move(pattern)), _opt(opt), _result(Tag::is_count) {
-    if (_pattern.empty() || _pattern.size() > XSG_MAX_PATTERN || _pattern.find('\n') != std::string::npos)
+    _regex_mode = _opt.pattern_mode == Options::PatternMode::REGEX ||
+                  (_opt.pattern_mode == Options::PatternMode::AUTO && use_str_as_regex(_pattern));
+    std::vector<std::string> literals{_pattern};
+    if (_regex_mode) {
+      if (_pattern.find('\n') != std::string::npos)
+        throw std::invalid_argument("xs::extern_search: a pattern must not contain '\\n'");
+      literals = required_literals(_pattern);  // throws std::invalid_argument when there is nothing to scan for
+      try {
+        _verifier = std::make_unique<LineVerifier>(_pattern, _opt.ignore_case);
+      } catch (const std::regex_error& e) {
+        throw std::invalid_argument(std::string("xs::extern_search: bad regular expression: ") + e.what());
+      }
+    } else if (_pattern.empty() || _pattern.size() > XSG_MAX_PATTERN || _pattern.find('\n') != std::string::npos) {
       throw std::invalid_argument("xs::extern_search: the GPU literal path needs a pattern of 1..64 bytes without '\\n'");
+    }
     _num_threads = num_threads < 1 ? 1 : num_threads;  // accepted for API compatibility; the search itself runs on the GPU
     _num_readers = max_num_readers < 1 ? 1 : max_num_readers;
     if (_opt.min_chunk == 0) _opt.min_chunk = XSG_DEFAULT_MIN_CHUNK;
@@ -234,14 +255,24 @@ class Searcher {
     _size = static_cast<uint64_t>(sb.st_size);
     try {
       plan(meta_file_path);
-      if (xsg_init(_opt.device, &_ctx) != XSG_OK) throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init"));
       xsg_scan_opts so{};
       so.flags = _opt.ignore_case ? XSG_SCAN_IGNORE_CASE : 0u;  // ASCII fold, like v1's tolower processor
-      if (xsg_stream_open(_ctx, reinterpret_cast<const uint8_t*>(_pattern.data()), static_cast<uint32_t>(_pattern.size()),
-                          Tag::kind, &so, &_stream) != XSG_OK)
-        throw std::runtime_error(detail::last_error("xs::extern_search: xsg_stream_open"));
+      // literal: one stream of the asked kind.  regex: one stream per required literal (each with a context of its
+      // own: the staging buffers belong to the context), reporting candidate lines with their indices
+      const uint32_t kinds = _regex_mode ? (XSG_LINE_BYTE_OFFSETS | XSG_LINE_INDICES) : Tag::kind;
+      for (const std::string& lit : literals) {
+        xsg_ctx* ctx = nullptr;
+        if (xsg_init(_opt.device, &ctx) != XSG_OK) throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init"));
+        _ctxs.push_back(ctx);
+        xsg_stream* st = nullptr;
+        if (xsg_stream_open(ctx, reinterpret_cast<const uint8_t*>(lit.data()), static_cast<uint32_t>(lit.size()), kinds, &so,
+                            &st) != XSG_OK)
+          throw std::runtime_error(detail::last_error("xs::extern_search: xsg_stream_open"));
+        _streams.push_back(st);
+      }
     } catch (...) {
-      if (_ctx) xsg_destroy(_ctx);
+      for (xsg_stream* st : _streams) xsg_stream_abort(st);
+      for (xsg_ctx* ctx : _ctxs) xsg_destroy(ctx);
       ::close(_fd);
       throw;
     }
@@ -251,9 +282,10 @@ class Searcher {
 
   ~Searcher() {
     join();
-    if (_stream) xsg_stream_abort(_stream);
+    for (xsg_stream* st : _streams)
+      if (st) xsg_stream_abort(st);
     _bufs.clear();
-    if (_ctx) xsg_destroy(_ctx);
+    for (xsg_ctx* ctx : _ctxs) xsg_destroy(ctx);
     if (_fd >= 0) ::close(_fd);
   }
 
@@ -396,6 +428,7 @@ class Searcher {
     std::unique_ptr<detail::Pinned> extra;  // or a one-off buffer (a carry longer than the headroom)
     const uint8_t* ptr = nullptr;           // first byte of the segment on the host
     uint64_t goff = 0;                      // its global file offset
+    uint64_t len = 0;                       // bytes of it that were pushed (whole chunks)
   };
 
   // ---- results of one finished part -> the result collector ------------------------------------------
@@ -419,6 +452,118 @@ class Searcher {
       for (uint64_t i = 0; i < n; ++i)
         out.emplace_back(reinterpret_cast<const char*>(seg.ptr) + (st[i] - seg.goff), static_cast<size_t>(ln[i]));
       _result.add(std::move(out));
+    }
+    return true;
+  }
+
+  // ---- regex mode: candidate lines of one finished part -> verified results --------------------------------
+  // Candidates are the lines the literal streams report, plus -- unconditionally -- the lines that reach into the
+  // last kZoneBytes of the segment: the literal scan reproduces the reference matcher's chunk-tail behaviour
+  // (DESIGN.md 4.3), which may skip an occurrence among the last 31+m positions of a chunk, and a regular
+  // expression (re2 in the reference) has no such tail.  Segments are pushed as ONE chunk in this mode, so that
+  // zone exists once per segment.
+  static constexpr uint64_t kZoneBytes = 32 + 2 * XSG_MAX_PATTERN;
+
+  struct Candidate {
+    uint64_t start, index;
+  };
+
+  bool harvest_regex(const std::vector<const xsg_result*>& rs, uint64_t part, const Inflight& seg) {
+    std::vector<Candidate> cand;
+    std::vector<uint64_t> off, idx;
+    for (const xsg_result* r : rs) {
+      const uint64_t n = xsg_result_part_count(r, part, XSG_LINE_BYTE_OFFSETS);
+      off.resize(n);
+      idx.resize(n);
+      if (n && (xsg_result_part_copy(r, part, XSG_LINE_BYTE_OFFSETS, off.data(), n) != XSG_OK ||
+                xsg_result_part_copy(r, part, XSG_LINE_INDICES, idx.data(), n) != XSG_OK))
+        return false;
+      for (uint64_t i = 0; i < n; ++i) cand.push_back({off[i], idx[i]});
+    }
+    const uint8_t* base = seg.ptr;
+    const uint64_t end = seg.len;
+    _newlines_seen += xsg_result_part_newlines(rs[0], part);  // '\n' in the file up to the end of this segment
+    {
+      uint64_t s0 = end > kZoneBytes ? end - kZoneBytes : 0;
+      while (s0 > 0 && base[s0 - 1] != '\n') --s0;  // start of the line holding the first zone byte
+      uint64_t index = _newlines_seen - static_cast<uint64_t>(std::count(base + s0, base + end, uint8_t('\n')));
+      for (uint64_t pos = s0; pos < end; ++index) {
+        cand.push_back({seg.goff + pos, index});
+        const void* nl = std::memchr(base + pos, '\n', static_cast<size_t>(end - pos));
+        if (!nl) break;
+        pos = static_cast<uint64_t>(static_cast<const uint8_t*>(nl) - base) + 1;
+      }
+    }
+    std::sort(cand.begin(), cand.end(), [](const Candidate& a, const Candidate& b) { return a.start < b.start; });
+    cand.erase(std::unique(cand.begin(), cand.end(), [](const Candidate& a, const Candidate& b) { return a.start == b.start; }),
+               cand.end());
+
+    // verification on up to num_threads host threads (what the reference's worker threads are left with)
+    constexpr bool kMatchLevel = Tag::kind == XSG_COUNT || Tag::kind == XSG_MATCH_BYTE_OFFSETS;
+    const size_t n = cand.size();
+    std::vector<uint64_t> line_len(n);
+    std::vector<uint8_t> keep(n, 0), terminated(n, 0);
+    std::vector<std::vector<uint64_t>> pos(kMatchLevel ? n : 0);
+    auto work = [&](size_t lo, size_t hi) {
+      for (size_t i = lo; i < hi; ++i) {
+        const uint64_t rel = cand[i].start - seg.goff;
+        const void* nl = std::memchr(base + rel, '\n', static_cast<size_t>(end - rel));
+        terminated[i] = nl != nullptr;
+        line_len[i] = nl ? static_cast<uint64_t>(static_cast<const uint8_t*>(nl) - (base + rel)) : end - rel;
+        const std::string_view line(reinterpret_cast<const char*>(base + rel), static_cast<size_t>(line_len[i]));
+        if constexpr (kMatchLevel) {
+          _verifier->match_positions(line, &pos[i]);
+          keep[i] = !pos[i].empty();
+        } else {
+          keep[i] = _verifier->matches(line);
+        }
+      }
+    };
+    const size_t nt = std::min<size_t>(static_cast<size_t>(_num_threads), n / 64 + 1);
+    if (nt <= 1) {
+      work(0, n);
+    } else {
+      std::vector<std::thread> pool;
+      for (size_t t = 0; t < nt; ++t) pool.emplace_back(work, n * t / nt, n * (t + 1) / nt);
+      for (auto& t : pool) t.join();
+    }
+
+    if constexpr (Tag::is_count) {
+      for (size_t i = 0; i < n; ++i) _running_total += kMatchLevel ? pos[i].size() : keep[i];
+      _result.add(std::vector<uint64_t>{_running_total});
+      _published = true;
+    } else if constexpr (std::is_same_v<value_type, uint64_t>) {
+      std::vector<uint64_t> v;
+      for (size_t i = 0; i < n; ++i) {
+        if (!keep[i]) continue;
+        if constexpr (Tag::kind == XSG_MATCH_BYTE_OFFSETS) {
+          for (uint64_t p : pos[i]) v.push_back(cand[i].start + p);
+        } else if constexpr (Tag::kind == XSG_LINE_INDICES) {
+          v.push_back(cand[i].index);
+        } else {
+          v.push_back(cand[i].start);
+        }
+      }
+      _result.add(std::move(v));
+    } else {
+      std::vector<std::string> out;
+      for (size_t i = 0; i < n; ++i)  // like the literal xs::lines: an unterminated last line is not a line
+        if (keep[i] && terminated[i])
+          out.emplace_back(reinterpret_cast<const char*>(base + (cand[i].start - seg.goff)), static_cast<size_t>(line_len[i]));
+      _result.add(std::move(out));
+    }
+    return true;
+  }
+
+  // results of every part that has finished since the last call (literal: one stream; regex: all of them)
+  template <class GetResult>
+  bool harvest_finished(GetResult&& result_of, uint64_t* parts_done, const Inflight& seg) {
+    std::vector<const xsg_result*> rs;
+    for (size_t k = 0; k < _streams.size(); ++k) rs.push_back(result_of(k));
+    while (*parts_done < xsg_result_num_parts(rs[0])) {
+      const bool ok = _regex_mode ? harvest_regex(rs, *parts_done, seg) : harvest(rs[0], *parts_done, seg);
+      if (!ok) return false;
+      ++*parts_done;
     }
     return true;
   }
@@ -519,32 +664,38 @@ class Searcher {
       }
       carry = cur.ptr + consumed;
       carry_len = seg_len - consumed;
+      cur.len = consumed;
       if (bounds.empty()) {  // nothing complete yet: everything is carried on
         carry_holder = std::move(cur);
         continue;
       }
-      if (xsg_stream_push(_stream, cur.ptr, consumed, bounds.data(), bounds.size(), nullptr) != XSG_OK)
-        throw std::runtime_error(detail::last_error("xsg_stream_push"));
+      if (_regex_mode) bounds.assign(1, consumed);  // re2 has no chunk-tail behaviour to reproduce (see harvest_regex)
+      for (xsg_stream* st : _streams)
+        if (xsg_stream_push(st, cur.ptr, consumed, bounds.data(), bounds.size(), nullptr) != XSG_OK)
+          throw std::runtime_error(detail::last_error("xsg_stream_push"));
       // the previous segment was scanned inside this push: publish its results, free its buffer
-      const xsg_result* res = xsg_stream_result(_stream);
-      while (parts_done < xsg_result_num_parts(res)) {
-        if (!harvest(res, parts_done, prev)) throw std::runtime_error(detail::last_error("result copy"));
-        ++parts_done;
-      }
+      if (!harvest_finished([&](size_t k) { return xsg_stream_result(_streams[k]); }, &parts_done, prev))
+        throw std::runtime_error(detail::last_error("result copy"));
       if (prev.valid) release(prev);
       prev = std::move(cur);
     }
-    xsg_result* fin = nullptr;
-    xsg_stream* st = _stream;
-    _stream = nullptr;  // close destroys it whatever happens
-    if (xsg_stream_close(st, &fin) != XSG_OK) throw std::runtime_error(detail::last_error("xsg_stream_close"));
-    bool ok = true;
-    while (ok && parts_done < xsg_result_num_parts(fin)) {
-      ok = harvest(fin, parts_done, prev);
-      ++parts_done;
+    std::vector<xsg_result*> fin(_streams.size(), nullptr);
+    bool closed = true;
+    for (size_t k = 0; k < _streams.size(); ++k) {
+      xsg_stream* st = _streams[k];
+      _streams[k] = nullptr;  // close destroys it whatever happens
+      closed = xsg_stream_close(st, &fin[k]) == XSG_OK && closed;
     }
-    xsg_result_timings(fin, &_timings);
-    xsg_result_free(fin);
+    const std::string close_error = closed ? std::string() : detail::last_error("xsg_stream_close");
+    bool ok = closed && harvest_finished([&](size_t k) { return static_cast<const xsg_result*>(fin[k]); }, &parts_done, prev);
+    if (fin[0]) xsg_result_timings(fin[0], &_timings);
+    for (xsg_result* r : fin)
+      if (r) xsg_result_free(r);
+    if (!closed) {
+      if (prev.valid) release(prev);
+      if (carry_holder.valid) release(carry_holder);
+      throw std::runtime_error(close_error);
+    }
     if (prev.valid) release(prev);
     if (carry_holder.valid) release(carry_holder);
     if (!ok) throw std::runtime_error(detail::last_error("result copy"));
@@ -562,9 +713,12 @@ class Searcher {
   std::vector<detail::Block> _blocks;
   uint64_t _max_block = 0, _headroom = 0;
 
-  xsg_ctx* _ctx = nullptr;
-  xsg_stream* _stream = nullptr;
+  std::vector<xsg_ctx*> _ctxs;        // literal: one; regex: one per required literal
+  std::vector<xsg_stream*> _streams;  // the stream of each context
   xsg_timings _timings{};
+  bool _regex_mode = false;
+  std::unique_ptr<LineVerifier> _verifier;
+  uint64_t _newlines_seen = 0;  // regex mode: '\n' in all harvested segments
 
   mutable std::mutex _m;  // guards _free, _ready, _next_block, _next_slice, _cur_buf, _slices_left, _error
   std::condition_variable _cv;

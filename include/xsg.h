@@ -171,6 +171,9 @@ uint64_t xsg_result_num_parts(const xsg_result* r);
 uint64_t xsg_result_part_count(const xsg_result* r, uint64_t part, uint32_t kind);
 int xsg_result_part_copy(const xsg_result* r, uint64_t part, uint32_t kind, uint64_t* dst, uint64_t cap);
 int xsg_result_part_copy_line_lengths(const xsg_result* r, uint64_t part, uint64_t* dst, uint64_t cap);
+/* '\n' in the bytes of one part (valid when XSG_LINE_INDICES was asked for): lets a host stage that adds lines of
+ * its own -- the regex prefilter of xsearch_b200/regex_prefilter.hpp -- number them like the device does */
+uint64_t xsg_result_part_newlines(const xsg_result* r, uint64_t part);
 /* device pointer of a result vector (stays valid until xsg_result_free) */
 const uint64_t* xsg_result_device_ptr(const xsg_result* r, uint32_t kind);
 uint64_t xsg_result_newlines(const xsg_result* r);        /* '\n' in the scanned bytes (line kinds) */

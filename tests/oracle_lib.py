@@ -131,3 +131,74 @@ def load(build: bool = True):
     ref_so = os.path.join(ORACLE_DIR, "_ref", "libxsref.so")
     ref = Checker(ref_so, "xsr_") if os.path.exists(ref_so) else None
     return oracle, ref
+
+
+class RegexRef:
+    """The reference's regex wrappers over its vendored re2 (oracle/_ref/libxsref_re.so, oracle/ref_regex_shim.cpp):
+    the checker of the regex prefilter.  line_indices / lines are derived from byte_offsets_line the way ref_shim.cpp
+    derives them for the literal wrappers (the reference snapshot has no regex twin of either)."""
+
+    BAD = (1 << 64) - 1  # re2 rejected the pattern
+
+    def __init__(self, path: str):
+        L = self.lib = C.CDLL(path)
+        vp, u64, i32 = C.c_void_p, C.c_uint64, C.c_int
+        L.xsr_re_count.restype, L.xsr_re_count.argtypes = u64, [vp, u64, C.c_char_p, i32, _PU64, u64, i32]
+        for name in ("xsr_re_match_byte_offsets", "xsr_re_line_byte_offsets"):
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = u64, [vp, u64, C.c_char_p, i32, _PU64, u64, _PU64, u64]
+
+    def count(self, buf, pattern: bytes, bounds, lines: bool, ignore_case: bool = False) -> int:
+        a, addr = Checker._buf(buf)
+        b = np.ascontiguousarray(bounds, dtype=np.uint64)
+        n = self.lib.xsr_re_count(addr, a.size, pattern, int(ignore_case), b.ctypes.data_as(_PU64), b.size, int(lines))
+        if n == self.BAD:
+            raise ValueError("re2 rejected %r" % pattern)
+        return n
+
+    def _vec(self, name, buf, pattern, bounds, ignore_case):
+        a, addr = Checker._buf(buf)
+        b = np.ascontiguousarray(bounds, dtype=np.uint64)
+        bp = b.ctypes.data_as(_PU64)
+        fn = getattr(self.lib, name)
+        n = fn(addr, a.size, pattern, int(ignore_case), bp, b.size, None, 0)
+        if n == self.BAD:
+            raise ValueError("re2 rejected %r" % pattern)
+        out = np.empty(n, dtype=np.uint64)
+        if n:
+            fn(addr, a.size, pattern, int(ignore_case), bp, b.size, out.ctypes.data_as(_PU64), n)
+        return out
+
+    def match_byte_offsets(self, buf, pattern, bounds, ignore_case=False):
+        return self._vec("xsr_re_match_byte_offsets", buf, pattern, bounds, ignore_case)
+
+    def line_byte_offsets(self, buf, pattern, bounds, ignore_case=False):
+        return self._vec("xsr_re_line_byte_offsets", buf, pattern, bounds, ignore_case)
+
+    def expected_output(self, buf, pattern, bounds, tag, ignore_case=False) -> str:
+        """What xsgrep --tag <tag> prints for this search."""
+        a, _ = Checker._buf(buf)
+        if tag == "count":
+            return "%d\n" % self.count(a, pattern, bounds, False, ignore_case)
+        if tag == "count_lines":
+            return "%d\n" % self.count(a, pattern, bounds, True, ignore_case)
+        if tag == "match_byte_offsets":
+            return "".join("%d\n" % int(x) for x in self.match_byte_offsets(a, pattern, bounds, ignore_case))
+        lo = self.line_byte_offsets(a, pattern, bounds, ignore_case)
+        if tag == "line_byte_offsets":
+            return "".join("%d\n" % int(x) for x in lo)
+        nl = np.flatnonzero(a == 10)
+        if tag == "line_indices":  # 0-based number of '\n' before the line
+            return "".join("%d\n" % int(i) for i in np.searchsorted(nl, lo, side="left"))
+        assert tag == "lines"
+        raw, out = a.tobytes(), []
+        for s in lo:
+            k = int(np.searchsorted(nl, s, side="left"))
+            if k < nl.size:  # like the literal xs::lines: an unterminated last line is dropped
+                out.append(raw[int(s):int(nl[k])].decode("latin-1") + "\n")
+        return "".join(out)
+
+
+def load_regex_ref():
+    so = os.path.join(ORACLE_DIR, "_ref", "libxsref_re.so")
+    return RegexRef(so) if os.path.exists(so) else None

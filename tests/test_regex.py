@@ -1,0 +1,220 @@
+"""Regular expressions over the GPU literal scan (include/xsearch_b200/regex_prefilter.hpp).
+
+Checker: the reference's own regex wrappers (search_wrappers.h:63-88,209-271) over its vendored re2, compiled where they
+lie into oracle/_ref/libxsref_re.so (oracle/ref_regex_shim.cpp), and the fixture tests/golden/regex_vectors.json made
+from it (tools/make_golden.py --regex) for boxes without that library.
+
+CPU part: the checker reproduces the reference's own known answers (search_wrappersTest.cpp:74-105); the fixture agrees
+with the checker; literal extraction; the host stage (required literals + std::regex over candidate lines, driven by
+tests/cpp/regex_host_check.cpp, which replaces the GPU scan by a host loop) agrees with the reference on every case.
+GPU part (-m gpu): `xsgrep -E` = xs::extern_search with a regular expression, every tag, against the same expectations."""
+import hashlib
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPP_DIR = os.path.join(ROOT, "xsearch_b200", "cpp")
+XSGREP = os.path.join(CPP_DIR, "xsgrep")
+GOLD = os.path.join(ROOT, "tests", "golden")
+TAGS = ["count", "count_lines", "match_byte_offsets", "line_byte_offsets", "line_indices", "lines"]
+
+
+def corpora():
+    """name -> bytes (np.uint8).  Deterministic: the library's host-side generator and hand-made hazards."""
+    import xsearch_b200 as xs
+    out = {}
+    p = xs.SynthParams.make(9, b"Sherlock", 30.0 / 2048)
+    out["synth"] = xs.synth_host(4096 * 400, p)  # 1.6 MB of English-like lines
+    out["dummy"] = np.fromfile(os.path.join(GOLD, "wrappers_dummy_text.bin"), dtype=np.uint8)
+    # hazards of the literal scan's chunk-tail emulation: "SSherlock" / "llock" in the last bytes of the
+    # file and of every 64 KiB segment, mixed case, an unterminated last line
+    rng = np.random.default_rng(11)
+    words = [b"Sherlock", b"SSherlock", b"She lock", b"sherlock", b"SHERLOCK", b"llock", b"lolock", b"She\tlock", b"abc",
+             b"Shelock", b"Sheerlock", b"holmes", b"x"]
+    lines = []
+    for _ in range(30000):
+        k = int(rng.integers(1, 6))
+        lines.append(b" ".join(words[int(i)] for i in rng.integers(0, len(words), k)))
+    out["hazard"] = np.frombuffer(b"\n".join(lines) + b"\nlast line SSherlock", dtype=np.uint8).copy()
+    return out
+
+
+# (corpus, pattern, ignore_case)
+CASES = [
+    ("dummy", b"(a[n|m]t)", False),            # the reference's own regex test pattern (search_wrappersTest.cpp:74-105)
+    ("synth", b"She[r ]lock", False),          # the pattern of the v1 golden vectors (xsearchTest.cpp:17-335)
+    ("synth", b"(a[n|l]d)", False),
+    ("synth", b"th(e|is|at)\\b", False),
+    ("synth", b"(?:Sherlock|which) [a-z]+", False),
+    ("synth", b"wh(ich|ere)|Sherlock", False),  # three required literals -> three GPU streams
+    ("synth", b"[A-Z][a-z]+lock", False),
+    ("synth", b"o{2}k", False),
+    ("synth", b"sHE[r ]LOCK", True),
+    ("hazard", b"She[r ]lock", False),
+    ("hazard", b"S+her?lock", False),
+    ("hazard", b"she[r\\t ]lock", True),
+    ("hazard", b"(SS|l)lock", False),
+]
+
+
+def case_key(corpus, pattern, icase):
+    return "%s|%s|%d" % (corpus, pattern.decode(), int(icase))
+
+
+def digest(text: str):
+    raw = text.encode("latin-1")
+    return {"n": raw.count(b"\n"), "sha256": hashlib.sha256(raw).hexdigest(), "head": text[:120]}
+
+
+def expected_from_ref(ref, buf, pattern, icase):
+    bounds = [buf.size]  # re2 has no chunk-dependent behaviour for line-local matches
+    return {tag: digest(ref.expected_output(buf, pattern, bounds, tag, icase)) for tag in TAGS}
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return json.load(open(os.path.join(GOLD, "regex_vectors.json")))
+
+
+@pytest.fixture(scope="module")
+def data():
+    return corpora()
+
+
+@pytest.fixture(scope="module")
+def xsgrep():
+    try:
+        subprocess.check_call(["make", "-s", "-C", CPP_DIR], stdout=subprocess.DEVNULL)
+    except (OSError, subprocess.CalledProcessError):
+        if not os.path.exists(XSGREP):
+            raise
+    return XSGREP
+
+
+@pytest.fixture(scope="module")
+def host_check(tmp_path_factory):
+    exe = tmp_path_factory.mktemp("bin") / "regex_host_check"
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-I" + os.path.join(ROOT, "include"), "-o", str(exe),
+                           os.path.join(ROOT, "tests", "cpp", "regex_host_check.cpp")])
+    return str(exe)
+
+
+def test_checker_reproduces_reference_kat():
+    """search_wrappersTest.cpp:74-105: offsets {2,151,197,507}, line offsets {0,113,176,460}, count 4."""
+    ref = oracle_lib.load_regex_ref()
+    if ref is None:
+        pytest.skip("oracle/_ref/libxsref_re.so not built (reference tree absent)")
+    buf = np.fromfile(os.path.join(GOLD, "wrappers_dummy_text.bin"), dtype=np.uint8)
+    b = [buf.size]
+    assert ref.match_byte_offsets(buf, b"(a[n|m]t)", b).tolist() == [2, 151, 197, 507]
+    assert ref.line_byte_offsets(buf, b"(a[n|m]t)", b).tolist() == [0, 113, 176, 460]
+    assert ref.count(buf, b"(a[n|m]t)", b, True) == 4
+    # chunking at line starts does not change a line-local result
+    cut = int(np.flatnonzero(buf == 10)[3]) + 1
+    assert ref.match_byte_offsets(buf, b"(a[n|m]t)", [cut, buf.size]).tolist() == [2, 151, 197, 507]
+
+
+def test_fixture_matches_checker(golden, data):
+    ref = oracle_lib.load_regex_ref()
+    if ref is None:
+        pytest.skip("oracle/_ref/libxsref_re.so not built (reference tree absent)")
+    for corpus, pattern, icase in CASES:
+        assert golden["cases"][case_key(corpus, pattern, icase)] == expected_from_ref(ref, data[corpus], pattern, icase)
+    for name, buf in data.items():
+        assert golden["corpora"][name] == hashlib.sha256(buf.tobytes()).hexdigest()
+
+
+def test_cases_are_not_trivial(golden):
+    for key, exp in golden["cases"].items():
+        assert exp["count_lines"]["head"] != "0\n", key
+        assert exp["count"]["n"] == 1 and exp["line_byte_offsets"]["n"] == exp["line_indices"]["n"]
+
+
+def test_required_literals(xsgrep):
+    def lits(p):
+        out = subprocess.run([xsgrep, "--required-literals", p], capture_output=True, text=True)
+        if out.returncode != 0:
+            return None
+        rows = out.stdout.splitlines()
+        return int(rows[0].split()[1]), [r[len("literal: "):] for r in rows[1:]]
+    assert lits("She[r ]lock") == (1, ["lock"])
+    assert lits("Sherlock") == (0, ["Sherlock"])           # plain text by the reference's rule (utils.h:17-24)
+    assert lits("wh(ich|ere)|Sherlock") == (1, ["ich", "ere", "Sherlock"])
+    assert lits("(?:Sherlock|which) [a-z]+") == (1, ["Sherlock", "which"])
+    assert lits("th(e|is|at)\\b") == (1, ["th"])
+    assert lits("colou?r") == (1, ["colo"])
+    assert lits("x" * 80 + "+") == (1, ["x" * 64])         # longer than the GPU's pattern limit: a prefix is still required
+    assert lits("a\\.b\\\\c") == (1, ["a.b\\c"])
+    assert lits("(abc|abcd|zabc)+") == (1, ["abc"])        # literals containing another one are redundant
+    for bad in ("a*", "[ab]+", "ab|cd|", "x|.", "(?i)abc", "(?=a)b", "(a)\\1", "a\\nb", "\\pL+a"):
+        assert lits(bad) is None, bad
+
+
+def test_host_stage_matches_reference(golden, data, host_check, tmp_path):
+    """Literal extraction + std::regex over the candidate lines == the reference's re2 wrappers, every tag."""
+    paths = {}
+    for name, buf in data.items():
+        paths[name] = tmp_path / (name + ".txt")
+        buf.tofile(paths[name])
+    for corpus, pattern, icase in CASES:
+        exp = golden["cases"][case_key(corpus, pattern, icase)]
+        for tag in TAGS:
+            out = subprocess.run([host_check, tag, pattern.decode(), str(paths[corpus])] + (["-i"] if icase else []),
+                                 capture_output=True)
+            assert out.returncode == 0, (pattern, out.stderr.decode())
+            assert digest(out.stdout.decode("latin-1")) == exp[tag], (corpus, pattern, icase, tag)
+
+
+@pytest.mark.gpu
+def test_extern_search_regex(golden, data, xsgrep, tmp_path):
+    """xs::extern_search with a regular expression: GPU scan for the required literals, host verification."""
+    paths = {}
+    for name, buf in data.items():
+        paths[name] = tmp_path / (name + ".txt")
+        buf.tofile(paths[name])
+    # small segments: many segment ends (where the unconditional tail candidates come from), carries across them
+    base = ["--min-chunk", "65536", "--segment-bytes", "262144"]
+    for corpus, pattern, icase in CASES:
+        exp = golden["cases"][case_key(corpus, pattern, icase)]
+        for tag in TAGS:
+            for extra in ([], ["--live", "--readers", "3", "-j", "4"]):
+                if extra and (tag in ("count_lines", "match_byte_offsets", "line_byte_offsets") or corpus == "synth"):
+                    continue  # live + several readers / threads: the hazard corpus, half of the tags (keeps the test short)
+                out = subprocess.run([xsgrep, "-E", "--tag", tag, *base, *extra, *(["-i"] if icase else []),
+                                      pattern.decode(), str(paths[corpus])], capture_output=True)
+                assert out.returncode == 0, (pattern, out.stderr.decode())
+                assert digest(out.stdout.decode("latin-1")) == exp[tag], (corpus, pattern, icase, tag, extra)
+    # the reference's rule picks the regex reading by itself; -F forces plain text
+    exp = golden["cases"][case_key("synth", b"She[r ]lock", False)]
+    out = subprocess.run([xsgrep, "--tag", "count", *base, "She[r ]lock", str(paths["synth"])], capture_output=True)
+    assert out.returncode == 0 and digest(out.stdout.decode()) == exp["count"]
+    out = subprocess.run([xsgrep, "-F", "--tag", "count", *base, "She[r ]lock", str(paths["synth"])], capture_output=True)
+    assert out.returncode == 0 and out.stdout == b"0\n"
+    # nothing to scan for -> a clear error before any work starts
+    out = subprocess.run([xsgrep, "-E", "[a-z]+", str(paths["synth"])], capture_output=True, text=True)
+    assert out.returncode == 1 and "no literal" in out.stderr
+
+
+@pytest.mark.gpu
+def test_extern_search_regex_against_checker_large(xsgrep, tmp_path):
+    """A 40 MB file with the default 16 MiB chunks, against the reference library itself where it travelled."""
+    ref = oracle_lib.load_regex_ref()
+    if ref is None:
+        pytest.skip("oracle/_ref/libxsref_re.so did not travel")
+    import xsearch_b200 as xs
+    p = xs.SynthParams.make(21, b"Sherlock", 30.0 / 8192)
+    buf = xs.synth_host(4096 * 10000, p)
+    path = tmp_path / "big.txt"
+    buf.tofile(path)
+    for pattern in (b"She[r ]lock", b"mo(rn|n)[a-z]+ "):
+        for tag in TAGS:
+            out = subprocess.run([xsgrep, "-E", "--tag", tag, "--segment-bytes", str(32 << 20), "--readers", "2", "-j", "4",
+                                  pattern.decode(), str(path)], capture_output=True)
+            assert out.returncode == 0, out.stderr.decode()
+            assert out.stdout.decode("latin-1") == ref.expected_output(buf, pattern, [buf.size], tag), (pattern, tag)

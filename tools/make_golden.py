@@ -7,6 +7,8 @@
   * kat.json      : the expected values those tests assert (file:line noted per entry)
   * ref_vectors.json : outputs of the reference's own code (oracle/_ref/libxsref.so) on small seeded
     adversarial inputs -- inputs are regenerated from the seed by tests/gen_cases.py
+  * regex_vectors.json (--regex): digests of what the reference's regex wrappers over its vendored re2
+    (oracle/_ref/libxsref_re.so) return for the cases of tests/test_regex.py, per result kind
 """
 import json
 import os
@@ -17,6 +19,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 REF = "/root/reference"
 GOLD = os.path.join(ROOT, "tests", "golden")
 
@@ -134,5 +137,25 @@ def main():
     print("golden: %d KAT groups, %d reference vectors, %d ignore-case vectors" % (len(kat) - 1, len(vecs), len(ivecs)))
 
 
+def main_regex():
+    import hashlib
+
+    import oracle_lib
+    import test_regex as T
+    ref = oracle_lib.load_regex_ref()
+    assert ref is not None, "build oracle/_ref/libxsref_re.so first (make -C oracle)"
+    data = T.corpora()
+    cases = {T.case_key(c, p, i): T.expected_from_ref(ref, data[c], p, i) for c, p, i in T.CASES}
+    json.dump({"generator": "tools/make_golden.py --regex: xs::search::regex::{count, byte_offsets_match, byte_offsets_line} "
+                            "(search_wrappers.h:63-88,209-271) over re2 @954656f, oracle/_ref/libxsref_re.so; per kind the number "
+                            "of output rows of `xsgrep --tag KIND`, their sha256 and first bytes",
+               "corpora": {k: hashlib.sha256(v.tobytes()).hexdigest() for k, v in data.items()}, "cases": cases},
+              open(os.path.join(GOLD, "regex_vectors.json"), "w"), indent=1)
+    print("golden: %d regex cases" % len(cases))
+
+
 if __name__ == "__main__":
-    main()
+    if "--regex" in sys.argv:
+        main_regex()
+    else:
+        main()

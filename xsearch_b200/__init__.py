@@ -48,7 +48,7 @@ EXPORTS = [
     "xsg_corpus_chunk", "xsg_corpus_set_bounds", "xsg_corpus_num_chunks", "xsg_corpus_get_bounds",
     "xsg_synth_host", "xsg_chunk_bounds_host", "xsg_scan", "xsg_search_host", "xsg_stream_open", "xsg_stream_push",
     "xsg_stream_wait_copied", "xsg_stream_result", "xsg_stream_close", "xsg_stream_abort", "xsg_result_num_parts",
-    "xsg_result_part_count", "xsg_result_part_copy", "xsg_result_part_copy_line_lengths", "xsg_result_count",
+    "xsg_result_part_count", "xsg_result_part_newlines", "xsg_result_part_copy", "xsg_result_part_copy_line_lengths", "xsg_result_count",
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
     "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_scan_summary_device", "xsg_result_rebase_from_table", "xsg_result_free",
     "xsg_exchange_create", "xsg_exchange_connect", "xsg_exchange_push", "xsg_result_rebase_exchanged", "xsg_exchange_totals",
@@ -128,6 +128,7 @@ def _load() -> C.CDLL:
         "xsg_stream_abort": (None, [vp]),
         "xsg_result_num_parts": (u64, [vp]),
         "xsg_result_part_count": (u64, [vp, u64, u32]),
+        "xsg_result_part_newlines": (u64, [vp, u64]),
         "xsg_result_part_copy": (i32, [vp, u64, u32, pu64, u64]),
         "xsg_result_part_copy_line_lengths": (i32, [vp, u64, pu64, u64]),
         "xsg_result_count": (u64, [vp, u32]),

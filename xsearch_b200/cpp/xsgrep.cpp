@@ -2,7 +2,12 @@
 // example/grep.cpp:66-80 and checkit.cpp).  Also the driver of the C++ API tests (tests/test_cpp_api.py).
 //
 //   xsgrep [--tag lines|count|count_lines|match_byte_offsets|line_byte_offsets|line_indices] [--meta FILE]
-//          [-j N] [--readers N] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D] [--live] [-i] PATTERN FILE
+//          [-j N] [--readers N] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D] [--live] [-i] [-E | -F]
+//          PATTERN FILE
+//   -E / -F read PATTERN as a regular expression / as plain text; default: the reference's rule (utils.h:17-24).
+//   A regular expression is searched by scanning for its required literals on the GPU and running the expression
+//   over the candidate lines on -j host threads (xsearch_b200/regex_prefilter.hpp).
+//   xsgrep --required-literals PATTERN   print how PATTERN would be read and the literals the GPU would scan for
 //   xsgrep --selftest-host          host-only checks of the result collector (no GPU needed)
 //   xsgrep --metafile-cat FILE      print a v1 meta file (the reference's metafile_cat.cpp:23-49)
 #include <xsearch_b200/xsearch.hpp>
@@ -114,7 +119,46 @@ int selftest_host() {
     return 1;
   } catch (const std::runtime_error&) {
   }
+  // regex prefilter: the literals every match must contain, and the per-line verification
+  {
+    using V = std::vector<std::string>;
+    if (xs::required_literals("She[r ]lock") != V{"lock"}) return 1;
+    if (xs::required_literals("(a[n|m]t)") != V{"a"}) return 1;
+    if (xs::required_literals("foo(bar|bazqux)+x?") != V{"foo"}) return 1;
+    if (xs::required_literals("(?:alpha|beta)[0-9]") != V{"alpha", "beta"}) return 1;
+    if (xs::required_literals("a{2}bc\\.d*") != V{"bc."}) return 1;
+    for (const char* bad : {"a*", "[ab]+", "x|.", "(?=a)b", "(a)\\1", "a\\nb"}) {
+      try {
+        xs::required_literals(bad);
+        return 1;
+      } catch (const std::invalid_argument&) {
+      }
+    }
+    if (!xs::use_str_as_regex("She[r ]lock") || xs::use_str_as_regex("Sherlock") || xs::use_str_as_regex("a(b")) return 1;
+    const xs::LineVerifier v("a[nm]t", false), vi("SHE[r ]lock", true);
+    std::vector<uint64_t> pos;
+    v.match_positions("an ant and an amt, anti", &pos);
+    if (pos != std::vector<uint64_t>{3, 14, 19} || v.matches("and") || !vi.matches("a sherLOCK")) return 1;
+    try {
+      xs::Options o;
+      o.pattern_mode = xs::Options::PatternMode::REGEX;
+      xs::extern_search<xs::count>("[ab]+", "/nonexistent", "", 1, 1, o);
+      return 1;
+    } catch (const std::invalid_argument&) {
+    }
+  }
   std::puts("selftest-host ok");
+  return 0;
+}
+
+int show_required_literals(const std::string& pattern) {
+  std::printf("regex: %d\n", xs::use_str_as_regex(pattern) ? 1 : 0);
+  try {
+    for (const std::string& lit : xs::required_literals(pattern)) std::printf("literal: %s\n", lit.c_str());
+  } catch (const std::invalid_argument& e) {
+    std::fprintf(stderr, "xsgrep: %s\n", e.what());
+    return 1;
+  }
   return 0;
 }
 
@@ -147,6 +191,9 @@ int main(int argc, char** argv) {
     };
     if (s == "--selftest-host") return selftest_host();
     else if (s == "--metafile-cat") return metafile_cat(next());
+    else if (s == "--required-literals") return show_required_literals(next());
+    else if (s == "-E" || s == "--regex") a.opt.pattern_mode = xs::Options::PatternMode::REGEX;
+    else if (s == "-F" || s == "--fixed-strings") a.opt.pattern_mode = xs::Options::PatternMode::LITERAL;
     else if (s == "--tag") a.tag = next();
     else if (s == "--meta") a.meta = next();
     else if (s == "-j") a.threads = std::atoi(next().c_str());

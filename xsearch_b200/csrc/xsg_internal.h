@@ -69,6 +69,7 @@ struct xsg_part {  // results of one device-resident scan (one streamed segment)
   uint64_t n_match = 0;  // entries in match_off / value of xs::count
   uint64_t n_line = 0;   // entries in line_off / line_idx / value of xs::count_lines
   uint64_t n_lines = 0;  // entries in line_start / line_len (xs::lines; may be n_line - 1)
+  uint64_t newlines = 0; // '\n' in the bytes of this part (counted when line indices are asked for)
 };
 
 namespace xsg {

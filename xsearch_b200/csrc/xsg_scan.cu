@@ -398,6 +398,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     part->n_match = h.sel_total[0];
     part->n_line = h.sel_total[1];
     part->n_lines = (kinds & XSG_LINES) ? h.sel_total[1] - (h.unterminated ? 1 : 0) : 0;
+    part->newlines = h.nl_total;
     st->newlines += h.nl_total;
   }
   float ms = 0;
