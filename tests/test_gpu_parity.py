@@ -544,6 +544,7 @@ def test_stream_interface_parts_and_errors(xs, ctx, oracle):
     for part in range(st.num_parts()):
         got_m.append(st.part_vector(part, xs.MATCH_BYTE_OFFSETS))
         got_i.append(st.part_vector(part, xs.LINE_INDICES))
+        assert st.part_newlines(part) == int(np.count_nonzero(segs[part] == 10))
     res = st.close()
     assert res.count(xs.COUNT) == exp_m.size
     assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp_m) and np.array_equal(res.vector(xs.LINE_INDICES), exp_i)

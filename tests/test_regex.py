@@ -218,3 +218,48 @@ def test_extern_search_regex_against_checker_large(xsgrep, tmp_path):
                                   pattern.decode(), str(path)], capture_output=True)
             assert out.returncode == 0, out.stderr.decode()
             assert out.stdout.decode("latin-1") == ref.expected_output(buf, pattern, [buf.size], tag), (pattern, tag)
+
+
+def _random_expression(rng, depth=0):
+    """A random expression of the supported grammar over a three-letter alphabet (dense matches, many overlaps)."""
+    def atom():
+        r = rng.random()
+        if r < 0.45 or depth > 2:
+            return "".join(rng.choice(list("abc")) for _ in range(int(rng.integers(1, 4))))
+        if r < 0.60:
+            return "[" + "".join(sorted(set(rng.choice(list("abc ")) for _ in range(2)))) + "]"
+        if r < 0.65:
+            return "."
+        inner = "|".join(_random_expression(rng, depth + 1) for _ in range(int(rng.integers(1, 4))))
+        return ("(?:" if rng.random() < 0.5 else "(") + inner + ")"
+    parts = []
+    for _ in range(int(rng.integers(1, 4))):
+        a = atom()
+        q = rng.random()
+        if q < 0.12:
+            a = (a if len(a) == 1 or a[0] in "([." else "(?:" + a + ")") + rng.choice(["*", "+", "?", "{2}", "{1,2}", "{0,1}", "+?"])
+        parts.append(a)
+    return "".join(parts)
+
+
+def test_prefilter_never_loses_a_line(host_check, tmp_path):
+    """Soundness of required_literals on random expressions: regex_host_check fails (exit 2) when a line matches the
+    expression but holds none of the literals; its line count must also equal Python's re on the same lines."""
+    import re
+    rng = np.random.default_rng(2024)
+    text = "\n".join("".join(rng.choice(list("abc "), p=[0.35, 0.3, 0.25, 0.1]) for _ in range(int(rng.integers(0, 40))))
+                     for _ in range(600)) + "\n"
+    path = tmp_path / "abc.txt"
+    path.write_text(text)
+    lines = text.split("\n")[:-1]
+    usable = 0
+    for _ in range(150):
+        expr = _random_expression(rng)
+        out = subprocess.run([host_check, "count_lines", expr, str(path)], capture_output=True, text=True)
+        if out.returncode == 1:  # no required literal: rejected, nothing to check
+            assert "no literal" in out.stderr or "not usable" in out.stderr, (expr, out.stderr)
+            continue
+        assert out.returncode == 0, (expr, out.stderr)
+        usable += 1
+        assert int(out.stdout) == sum(1 for ln in lines if re.search(expr, ln)), expr
+    assert usable > 60

@@ -189,6 +189,10 @@ class Stream:
     def part_count(self, part: int, kind: int) -> int:
         return int(lib.xsg_result_part_count(lib.xsg_stream_result(self._h), part, kind))
 
+    def part_newlines(self, part: int) -> int:
+        """'\\n' in the bytes of one finished part (valid when LINE_INDICES was asked for)."""
+        return int(lib.xsg_result_part_newlines(lib.xsg_stream_result(self._h), part))
+
     def part_vector(self, part: int, kind: int) -> np.ndarray:
         res = lib.xsg_stream_result(self._h)
         n = int(lib.xsg_result_part_count(res, part, kind))
