@@ -15,9 +15,10 @@
 // across a '\n' ("a[^b]c", "a\sb") is searched line by line (documented difference to the reference, whose re2
 // call sees whole chunks).
 //
-// The expression syntax is the ECMAScript grammar of <regex> restricted to what re2 reads the same way:
-// literals, escapes, classes, '.', groups "(...)" / "(?:...)", alternation, the quantifiers * + ? {n,m} and
-// their lazy forms, the anchors ^ $ \b.  Look-around, back-references and re2's "(?flags)" are rejected.
+// The expression syntax is what re2 and the ECMAScript grammar of <regex> read the same way: literals, escapes,
+// classes, '.', groups "(...)" / "(?:...)", alternation, the quantifiers * + ? {n,m} and their lazy forms, the
+// anchors ^ $ \b.  Look-around, back-references and re2's "(?flags)" are rejected.  Matching follows re2's rules
+// (regex_vm.hpp); quantifiers bind to the last BYTE of a non-ASCII literal (re2: to the whole UTF-8 character).
 #pragma once
 
 #include <algorithm>
@@ -27,6 +28,8 @@
 #include <string>
 #include <string_view>
 #include <vector>
+
+#include "regex_vm.hpp"
 
 namespace xs {
 
@@ -324,27 +327,30 @@ inline std::vector<std::string> required_literals(const std::string& pattern) {
   return keep;
 }
 
-// Step 3: the expression over one candidate line (the bytes between two '\n', the '\n' excluded).
+// Step 3: the expression over one candidate line (the bytes between two '\n', the '\n' excluded), on the Pike VM of
+// regex_vm.hpp (re2's matching rules; <regex> is only used for the reference's dispatch rule above).
 class LineVerifier {
  public:
-  LineVerifier(const std::string& pattern, bool ignore_case)
-      : _re(pattern, ignore_case ? std::regex::ECMAScript | std::regex::icase | std::regex::optimize
-                                 : std::regex::ECMAScript | std::regex::optimize) {}
+  LineVerifier(const std::string& pattern, bool ignore_case) : _prog(pattern, ignore_case) {}
 
   bool matches(std::string_view line) const {
-    return std::regex_search(line.data(), line.data() + line.size(), _re);
+    regex_vm::Span m;
+    return _prog.search(line.data(), line.size(), 0, &m);
   }
 
-  // start of every match, left to right, non-overlapping (the loop of search_wrappers.h:63-88 within one line)
+  // start of every match, left to right, non-overlapping: the loop of search_wrappers.h:63-88 within one line.
+  // Like that loop (input.remove_prefix(shift)), the search for the next match sees the text BEHIND the previous
+  // match only: "^" and "\b" treat that position as a start of text ("\bfoo" finds two matches in "foofoo").
   void match_positions(std::string_view line, std::vector<uint64_t>* out) const {
-    const char* b = line.data();
-    const char* e = b + line.size();
-    for (std::cregex_iterator it(b, e, _re), end; it != end; ++it)
-      if (it->length(0) > 0) out->push_back(static_cast<uint64_t>(it->position(0)));
+    regex_vm::Span m;
+    for (size_t from = 0; from < line.size() && _prog.search(line.data() + from, line.size() - from, 0, &m);) {
+      if (m.end > m.begin) out->push_back(static_cast<uint64_t>(from + m.begin));
+      from += m.end > m.begin ? m.end : m.end + 1;  // an expression with a required literal never matches empty
+    }
   }
 
  private:
-  std::regex _re;
+  regex_vm::Program _prog;
 };
 
 }  // namespace xs

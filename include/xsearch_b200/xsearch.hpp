@@ -233,11 +233,7 @@ class Searcher {
       if (_pattern.find('\n') != std::string::npos)
         throw std::invalid_argument("xs::extern_search: a pattern must not contain '\\n'");
       literals = required_literals(_pattern);  // throws std::invalid_argument when there is nothing to scan for
-      try {
-        _verifier = std::make_unique<LineVerifier>(_pattern, _opt.ignore_case);
-      } catch (const std::regex_error& e) {
-        throw std::invalid_argument(std::string("xs::extern_search: bad regular expression: ") + e.what());
-      }
+      _verifier = std::make_unique<LineVerifier>(_pattern, _opt.ignore_case);  // std::invalid_argument: unsupported syntax
     } else if (_pattern.empty() || _pattern.size() > XSG_MAX_PATTERN || _pattern.find('\n') != std::string::npos) {
       throw std::invalid_argument("xs::extern_search: the GPU literal path needs a pattern of 1..64 bytes without '\\n'");
     }

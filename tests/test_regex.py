@@ -263,3 +263,62 @@ def test_prefilter_never_loses_a_line(host_check, tmp_path):
         usable += 1
         assert int(out.stdout) == sum(1 for ln in lines if re.search(expr, ln)), expr
     assert usable > 60
+
+
+def _random_rich_expression(rng, depth=0):
+    """Random expression using everything the VM supports: classes, ranges, negation, perl classes, '.', word
+    boundaries, anchors, greedy / lazy / counted repetition, nested groups and alternation."""
+    def atom():
+        r = rng.random()
+        if r < 0.40 or depth > 2:
+            return "".join(rng.choice(list("abcAB1")) for _ in range(int(rng.integers(1, 4))))
+        if r < 0.50:
+            return rng.choice(["[a-c]", "[^ab]", "[ab1]", "[A-Ca]", "[^a-c ]", "[\\w]", "[^\\d]", "[a\\-c]", "[[:digit:]b]"])
+        if r < 0.58:
+            return rng.choice(["\\w", "\\d", "\\s", "\\W", "\\D", "\\S", "."])
+        if r < 0.64:
+            return rng.choice(["\\b", "\\B", "^", "$"])
+        inner = "|".join(_random_rich_expression(rng, depth + 1) for _ in range(int(rng.integers(1, 4))))
+        return ("(?:" if rng.random() < 0.5 else "(") + inner + ")"
+    parts = []
+    for _ in range(int(rng.integers(1, 5))):
+        a = atom()
+        if rng.random() < 0.25 and a not in ("\\b", "\\B", "^", "$"):
+            if not (len(a) == 1 or a[0] in "([.\\"):
+                a = "(?:" + a + ")"
+            a += rng.choice(["*", "+", "?", "{2}", "{1,2}", "{0,1}", "{2,}", "+?", "*?", "??", "{1,3}?"])
+        parts.append(a)
+    return "".join(parts)
+
+
+def test_vm_matches_re2_on_random_expressions(host_check, tmp_path):
+    """The host matcher (regex_vm.hpp) against the reference's re2 wrappers: start offsets of all non-overlapping
+    matches, line by line (a single line has no chunk- or newline-dependent behaviour in the reference either)."""
+    ref = oracle_lib.load_regex_ref()
+    if ref is None:
+        pytest.skip("oracle/_ref/libxsref_re.so not built (reference tree absent)")
+    rng = np.random.default_rng(int(os.environ.get("XS_REGEX_SEED", "77")))
+    alphabet, weights = list("abcAB1 _") + ["é", "€"], [0.25, 0.2, 0.15, 0.08, 0.07, 0.08, 0.1, 0.03, 0.02, 0.02]
+    lines = ["".join(rng.choice(alphabet, p=weights) for _ in range(int(rng.integers(1, 30)))) for _ in range(250)]
+    raw_lines = [ln.encode("utf-8") for ln in lines]
+    path = tmp_path / "rich.txt"
+    path.write_bytes(b"\n".join(raw_lines) + b"\n")
+    starts = np.cumsum([0] + [len(r) + 1 for r in raw_lines])
+    checked = 0
+    for k in range(220):
+        expr = _random_rich_expression(rng)
+        icase = k % 5 == 0
+        out = subprocess.run([host_check, "match_byte_offsets", expr, str(path)] + (["-i"] if icase else []),
+                             capture_output=True, text=True)
+        if out.returncode == 1:  # no required literal (or syntax the VM rejects): nothing to compare
+            continue
+        assert out.returncode == 0, (expr, out.stderr)
+        try:
+            exp = [int(starts[i]) + int(x) for i, r in enumerate(raw_lines)
+                   for x in ref.match_byte_offsets(r, expr.encode(), [len(r)], icase)]
+        except ValueError:  # re2 rejects it
+            continue
+        got = [int(x) for x in out.stdout.split()]
+        assert got == exp, (expr, icase)
+        checked += 1
+    assert checked > 60, checked
