@@ -23,6 +23,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <memory>
 #include <regex>
 #include <stdexcept>
 #include <string>
@@ -337,6 +338,12 @@ class LineVerifier {
     regex_vm::Span m;
     return _prog.search(line.data(), line.size(), 0, &m);
   }
+
+  // The same answer from a lazily built DFA (regex_vm::Dfa), several times faster per byte.  The cache is not
+  // thread-safe: every verification thread owns one and passes it in.
+  using Cache = regex_vm::Dfa;
+  std::unique_ptr<Cache> make_cache() const { return std::make_unique<Cache>(_prog); }
+  static bool matches(std::string_view line, Cache& cache) { return cache.matches(line.data(), line.size()); }
 
   // start of every match, left to right, non-overlapping: the loop of search_wrappers.h:63-88 within one line.
   // Like that loop (input.remove_prefix(shift)), the search for the next match sees the text BEHIND the previous

@@ -16,11 +16,13 @@
 // letter escapes, non-ASCII class members, repetition counts above 1000.
 #pragma once
 
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 namespace xs::regex_vm {
@@ -372,6 +374,12 @@ class Program {
   }
 
   size_t size() const { return _prog.size(); }
+  // true when the program holds ^ $ \b \B: what follows a position then depends on its neighbours (no DFA)
+  bool has_assertions() const {
+    for (const Inst& i : _prog)
+      if (i.op == Inst::BOL || i.op == Inst::EOL || i.op == Inst::WORDB || i.op == Inst::NWORDB) return true;
+    return false;
+  }
 
   // Leftmost match starting at or behind `from` in the line [s, s+n); assertions see the whole line.
   bool search(const char* s, size_t n, size_t from, Span* out) const;
@@ -515,6 +523,7 @@ class Program {
       for (int c = 0; c < 256; ++c) _first[c] = first.has(unsigned(c));
   }
 
+  friend class Dfa;
   std::vector<Inst> _prog;
   std::vector<ByteSet> _sets;
   bool _has_first = false;
@@ -627,5 +636,130 @@ inline bool Program::search(const char* text, size_t n, size_t from, Span* out) 
   }
   return matched;
 }
+
+// ---- lazy DFA: does the line hold a match at all? --------------------------------------------------------------
+// For the line kinds (count_lines, line_byte_offsets, line_indices, lines) only the existence of a match counts, and
+// existence does not depend on priorities: the set of program counters alive after each byte is a DFA state.  States
+// and transitions are built on first use (the classic lazy subset construction, as in re2's DFA), one table row of
+// 256 entries per state, at most kMaxStates states (then the cache is flushed).  Not thread-safe: one Dfa per
+// verification thread; the Program is shared.  Programs with assertions are answered by the Pike VM.
+class Dfa {
+ public:
+  explicit Dfa(const Program& p) : _p(p), _usable(!p.has_assertions()) {
+    if (_usable) reset();
+  }
+
+  bool matches(const char* text, size_t n) {
+    if (!_usable) {
+      Span m;
+      return _p.search(text, n, 0, &m);
+    }
+    const unsigned char* s = reinterpret_cast<const unsigned char*>(text);
+    int32_t st = _start;
+    if (_accept[size_t(st)]) return true;
+    for (size_t i = 0; i < n; ++i) {
+      if (st == _start && _p._has_first) {  // nothing in flight: skip to the next byte a match can start with
+        while (i < n && !_p._first[s[i]]) ++i;
+        if (i >= n) break;
+      }
+      int32_t nx = _next[size_t(st) * 256 + s[i]];  // the accept flag travels in the table entry: one load per byte
+      if (nx < 0) nx = step(st, s[i]);
+      if (nx & kAcceptBit) return true;
+      st = nx;
+    }
+    return false;
+  }
+
+  size_t states() const { return _sets.size(); }
+
+ private:
+  static constexpr size_t kMaxStates = 2048;
+  static constexpr int32_t kAcceptBit = 1 << 30;
+
+  void reset() {
+    _sets.clear();
+    _accept.clear();
+    _next.clear();
+    _index.clear();
+    _mark.assign(_p._prog.size(), 0);
+    _epoch = 0;
+    std::vector<uint32_t> set;
+    bool acc = false;
+    begin_set();
+    closure(0, &set, &acc);
+    _start = intern(std::move(set), acc);
+  }
+
+  void begin_set() {
+    if (++_epoch == 0) {  // wrapped: clear the marks
+      std::fill(_mark.begin(), _mark.end(), 0);
+      _epoch = 1;
+    }
+  }
+
+  // consuming instructions reachable from pc without reading a byte; *acc when MATCH is among them
+  void closure(uint32_t pc0, std::vector<uint32_t>* set, bool* acc) {
+    _stack.clear();
+    _stack.push_back(pc0);
+    while (!_stack.empty()) {
+      const uint32_t pc = _stack.back();
+      _stack.pop_back();
+      if (_mark[pc] == _epoch) continue;
+      _mark[pc] = _epoch;
+      const Inst& i = _p._prog[pc];
+      switch (i.op) {
+        case Inst::JMP: _stack.push_back(i.x); break;
+        case Inst::SPLIT: _stack.push_back(i.y), _stack.push_back(i.x); break;
+        case Inst::MATCH: *acc = true; break;
+        default: set->push_back(pc); break;  // BYTE, SET (no assertions in a usable program)
+      }
+    }
+  }
+
+  int32_t intern(std::vector<uint32_t>&& set, bool acc) {
+    std::sort(set.begin(), set.end());
+    std::string key(reinterpret_cast<const char*>(set.data()), set.size() * sizeof(uint32_t));
+    key.push_back(acc ? 1 : 0);
+    auto it = _index.find(key);
+    if (it != _index.end()) return it->second;
+    const int32_t id = static_cast<int32_t>(_sets.size());
+    _sets.push_back(std::move(set));
+    _accept.push_back(acc ? 1 : 0);
+    _next.resize(_next.size() + 256, -1);
+    _index.emplace(std::move(key), id);
+    return id;
+  }
+
+  int32_t step(int32_t st, unsigned char c) {
+    std::vector<uint32_t> set;
+    bool acc = false;
+    begin_set();
+    for (uint32_t pc : _sets[size_t(st)]) {
+      const Inst& i = _p._prog[pc];
+      if ((i.op == Inst::BYTE && i.byte == c) || (i.op == Inst::SET && _p._sets[i.x].has(c))) closure(pc + 1, &set, &acc);
+    }
+    closure(0, &set, &acc);  // a match may start at the next byte as well
+    if (_sets.size() >= kMaxStates) {  // cache full: start over (the current transition is rebuilt below)
+      std::vector<uint32_t> cur = _sets[size_t(st)];
+      const bool cur_acc = _accept[size_t(st)] != 0;
+      reset();
+      st = intern(std::move(cur), cur_acc);
+    }
+    int32_t nx = intern(std::move(set), acc);
+    if (acc) nx |= kAcceptBit;  // the search ends there, so the flagged value is never used as a state
+    _next[size_t(st) * 256 + c] = nx;
+    return nx;
+  }
+
+  const Program& _p;
+  const bool _usable;
+  int32_t _start = 0;
+  std::vector<std::vector<uint32_t>> _sets;  // state -> its program counters (sorted)
+  std::vector<uint8_t> _accept;
+  std::vector<int32_t> _next;                // state x byte -> state, -1 = not built yet
+  std::unordered_map<std::string, int32_t> _index;
+  std::vector<uint32_t> _mark, _stack;
+  uint32_t _epoch = 0;
+};
 
 }  // namespace xs::regex_vm

@@ -500,7 +500,8 @@ class Searcher {
     std::vector<uint64_t> line_len(n);
     std::vector<uint8_t> keep(n, 0), terminated(n, 0);
     std::vector<std::vector<uint64_t>> pos(kMatchLevel ? n : 0);
-    auto work = [&](size_t lo, size_t hi) {
+    auto work = [&](size_t thread, size_t lo, size_t hi) {
+      LineVerifier::Cache& cache = *_caches[thread];
       for (size_t i = lo; i < hi; ++i) {
         const uint64_t rel = cand[i].start - seg.goff;
         const void* nl = std::memchr(base + rel, '\n', static_cast<size_t>(end - rel));
@@ -511,16 +512,17 @@ class Searcher {
           _verifier->match_positions(line, &pos[i]);
           keep[i] = !pos[i].empty();
         } else {
-          keep[i] = _verifier->matches(line);
+          keep[i] = LineVerifier::matches(line, cache);
         }
       }
     };
     const size_t nt = std::min<size_t>(static_cast<size_t>(_num_threads), n / 64 + 1);
+    while (_caches.size() < nt) _caches.push_back(_verifier->make_cache());  // one lazy DFA per verification thread
     if (nt <= 1) {
-      work(0, n);
+      work(0, 0, n);
     } else {
       std::vector<std::thread> pool;
-      for (size_t t = 0; t < nt; ++t) pool.emplace_back(work, n * t / nt, n * (t + 1) / nt);
+      for (size_t t = 0; t < nt; ++t) pool.emplace_back(work, t, n * t / nt, n * (t + 1) / nt);
       for (auto& t : pool) t.join();
     }
 
@@ -714,6 +716,7 @@ class Searcher {
   xsg_timings _timings{};
   bool _regex_mode = false;
   std::unique_ptr<LineVerifier> _verifier;
+  std::vector<std::unique_ptr<LineVerifier::Cache>> _caches;  // regex mode: per verification thread, kept across parts
   uint64_t _newlines_seen = 0;  // regex mode: '\n' in all harvested segments
 
   mutable std::mutex _m;  // guards _free, _ready, _next_block, _next_slice, _cur_buf, _slices_left, _error

@@ -35,6 +35,7 @@ int main(int argc, char** argv) {
     return 1;
   }
   const xs::LineVerifier v(pattern, icase);
+  const auto cache = v.make_cache();  // the lazy DFA the Searcher uses for the line kinds
   uint64_t count = 0, count_lines = 0, index = 0;
   std::string out;
   for (size_t pos = 0; pos < data.size(); ++index) {
@@ -45,6 +46,14 @@ int main(int argc, char** argv) {
     for (const auto& l : lits) candidate = candidate || holds(line, l, icase);
     std::vector<uint64_t> at;
     if (candidate) v.match_positions(line, &at);
+    if (xs::LineVerifier::matches(line, *cache) != v.matches(line)) {
+      std::fprintf(stderr, "line %llu: the DFA and the VM disagree\n", (unsigned long long)index);
+      return 3;
+    }
+    if (candidate && at.empty() == v.matches(line)) {
+      std::fprintf(stderr, "line %llu: match_positions and matches disagree\n", (unsigned long long)index);
+      return 3;
+    }
     if (!candidate && v.matches(line)) {  // the prefilter would have lost this line
       std::fprintf(stderr, "line %llu matches but holds no required literal\n", (unsigned long long)index);
       return 2;
