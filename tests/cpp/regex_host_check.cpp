@@ -1,7 +1,7 @@
 // regex_host_check -- TEST DRIVER for the host stage of the regex prefilter (include/xsearch_b200/regex_prefilter.hpp).
 // Not part of the product: it hands EVERY line of a file that holds a required literal (found with memmem) to
 // xs::LineVerifier, i.e. it replaces the GPU literal scan by a trivial host loop so that the literal extraction and the
-// std::regex verification can be pinned against the reference's re2 wrappers on a machine without a GPU
+// VM / DFA verification (regex_vm.hpp) can be pinned against the reference's re2 wrappers on a machine without a GPU
 // (tests/test_regex.py).  Prints what `xsgrep -E --tag TAG` prints.
 #include <xsearch_b200/regex_prefilter.hpp>
 

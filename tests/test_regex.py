@@ -5,7 +5,7 @@ lie into oracle/_ref/libxsref_re.so (oracle/ref_regex_shim.cpp), and the fixture
 from it (tools/make_golden.py --regex) for boxes without that library.
 
 CPU part: the checker reproduces the reference's own known answers (search_wrappersTest.cpp:74-105); the fixture agrees
-with the checker; literal extraction; the host stage (required literals + std::regex over candidate lines, driven by
+with the checker; literal extraction; the host stage (required literals + our regex VM / lazy DFA over candidate lines, driven by
 tests/cpp/regex_host_check.cpp, which replaces the GPU scan by a host loop) agrees with the reference on every case.
 GPU part (-m gpu): `xsgrep -E` = xs::extern_search with a regular expression, every tag, against the same expectations."""
 import hashlib
@@ -157,7 +157,7 @@ def test_required_literals(xsgrep):
 
 
 def test_host_stage_matches_reference(golden, data, host_check, tmp_path):
-    """Literal extraction + std::regex over the candidate lines == the reference's re2 wrappers, every tag."""
+    """Literal extraction + xs::LineVerifier (regex_vm.hpp) over the candidate lines == the reference's re2 wrappers, every tag."""
     paths = {}
     for name, buf in data.items():
         paths[name] = tmp_path / (name + ".txt")
