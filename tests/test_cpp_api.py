@@ -104,8 +104,7 @@ def run_xsgrep(xsgrep, tag, pat, path, extra=()):
     return out.stdout.decode("latin-1")
 
 
-@pytest.mark.gpu
-def test_extern_search_all_tags(xsgrep, tmp_path):
+def check_all_tags(xsgrep, tmp_path):
     import xsearch_b200 as xs
     oracle, _ = oracle_lib.load(build=False)
     p = xs.SynthParams.make(9, b"Sherlock", 30.0 / 8192)
@@ -122,8 +121,7 @@ def test_extern_search_all_tags(xsgrep, tmp_path):
             assert run_xsgrep(xsgrep, tag, pat, path, base + ["--live", "--readers", "3", "-j", "4"]) == exp, (tag, pat, "live")
 
 
-@pytest.mark.gpu
-def test_extern_search_with_meta_file(xsgrep, tmp_path):
+def check_with_meta_file(xsgrep, tmp_path):
     import xsearch_b200 as xs
     oracle, _ = oracle_lib.load(build=False)
     import gen_cases
@@ -150,8 +148,7 @@ def test_extern_search_with_meta_file(xsgrep, tmp_path):
     assert out.returncode != 0 and "compressed" in out.stderr
 
 
-@pytest.mark.gpu
-def test_extern_search_edge_files(xsgrep, tmp_path):
+def check_edge_files(xsgrep, tmp_path):
     oracle, _ = oracle_lib.load(build=False)
     rng = np.random.default_rng(3)
     import gen_cases
@@ -175,8 +172,7 @@ def test_extern_search_edge_files(xsgrep, tmp_path):
             assert run_xsgrep(xsgrep, tag, b"needle", path, base + ["--live"]) == exp, (name, tag)
 
 
-@pytest.mark.gpu
-def test_extern_search_ignore_case(xsgrep, tmp_path):
+def check_ignore_case(xsgrep, tmp_path):
     """The ignore_case overloads (README.md:37, example/grep.cpp:69-77): lines come back with their ORIGINAL bytes."""
     oracle, _ = oracle_lib.load(build=False)
     text = (b"Sherlock holmes\nno match here\nSHERLOCK again, sherlock twice\nshErLoCk\n" * 3000)
@@ -195,7 +191,32 @@ def test_extern_search_ignore_case(xsgrep, tmp_path):
     assert run_xsgrep(xsgrep, "count", b"SherLOCK", path, base[:-1]) == "0\n"
 
 
-@pytest.mark.gpu
-def test_extern_search_errors(xsgrep, tmp_path):
+def check_errors(xsgrep, tmp_path):
     out = subprocess.run([xsgrep, "abc", str(tmp_path / "missing.txt")], capture_output=True, text=True)
     assert out.returncode == 1 and "cannot open" in out.stderr
+
+
+# the same checks run on the CPU against the test double of the C ABI in tests/test_host_pipeline.py
+@pytest.mark.gpu
+def test_extern_search_all_tags(xsgrep, tmp_path):
+    check_all_tags(xsgrep, tmp_path)
+
+
+@pytest.mark.gpu
+def test_extern_search_with_meta_file(xsgrep, tmp_path):
+    check_with_meta_file(xsgrep, tmp_path)
+
+
+@pytest.mark.gpu
+def test_extern_search_edge_files(xsgrep, tmp_path):
+    check_edge_files(xsgrep, tmp_path)
+
+
+@pytest.mark.gpu
+def test_extern_search_ignore_case(xsgrep, tmp_path):
+    check_ignore_case(xsgrep, tmp_path)
+
+
+@pytest.mark.gpu
+def test_extern_search_errors(xsgrep, tmp_path):
+    check_errors(xsgrep, tmp_path)

@@ -1,0 +1,234 @@
+"""The host pipeline of xs::extern_search (include/xsearch_b200/xsearch.hpp) on the CPU, against a TEST DOUBLE of the C ABI.
+
+The GPU tests of tests/test_cpp_api.py and tests/test_regex.py drive `xsgrep` (the C++20 layer over libxsg.so) on a
+B200.  Everything above the C ABI is host logic -- reader threads that pread slices of the same segment, the v1 chunk
+rule applied to segments, carries across segment edges (also longer than the headroom), recycling of the pinned
+buffers, the live iterator, the regex host stage, the failure path -- and a container without a GPU can check it when
+the C ABI underneath answers: tests/cpp/xsg_testdouble.cpp implements the 17 entry points the header calls with the CPU
+oracle and reads every pushed segment LATE (inside the next push, like the real library's scan), comparing a checksum
+taken at push time, so a buffer recycled too early is an error and not luck.
+
+The double lives under tests/, is built into tests/cpp/_build/ and is linked only into the copy of the driver built
+there (xsgrep_double); the product (xsearch_b200/cpp/xsgrep, libxsg.so) never sees it.  The same check functions run
+here against the double and, marked gpu, against the real library: whatever passes here and fails there is a
+difference between the double and the CUDA path, not a host-pipeline bug.
+
+Also here: the same driver under ThreadSanitizer (readers + pusher + verification threads + a live consumer), and the
+failure path (an injected push failure closes the result, reports the error, leaves no thread behind)."""
+import os
+import shutil
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib
+import test_cpp_api as capi
+import test_regex as rx
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPP = os.path.join(ROOT, "tests", "cpp")
+OUT = os.path.join(CPP, "_build")
+SOURCES = [os.path.join(ROOT, "xsearch_b200", "cpp", "xsgrep.cpp"), os.path.join(CPP, "xsg_testdouble.cpp")]
+HEADERS = [os.path.join(ROOT, "include", "xsg.h"), os.path.join(ROOT, "oracle", "xs_oracle.c"),
+           os.path.join(ROOT, "oracle", "xs_oracle.h")] + \
+          [os.path.join(ROOT, "include", "xsearch_b200", f) for f in sorted(os.listdir(os.path.join(ROOT, "include", "xsearch_b200")))]
+
+
+def _build(name, flags):
+    """xsgrep.cpp + the test double + the oracle's C restatement in one executable (no libxsg.so involved)."""
+    os.makedirs(OUT, exist_ok=True)
+    exe = os.path.join(OUT, name)
+    newest = max(os.path.getmtime(p) for p in SOURCES + HEADERS)
+    if os.path.exists(exe) and os.path.getmtime(exe) >= newest:
+        return exe
+    obj = os.path.join(OUT, name + ".oracle.o")
+    subprocess.check_call(["gcc", "-O2", "-c", *[f for f in flags if f.startswith("-fsanitize") or f == "-g"],
+                           "-o", obj, os.path.join(ROOT, "oracle", "xs_oracle.c")])
+    subprocess.check_call(["g++", "-std=c++20", "-Wall", "-Wextra", "-pthread", *flags, "-I" + os.path.join(ROOT, "include"),
+                           "-o", exe, *SOURCES, obj])
+    return exe
+
+
+@pytest.fixture(scope="module")
+def double():
+    return _build("xsgrep_double", ["-O2"])
+
+
+@pytest.fixture(scope="module")
+def double_tsan():
+    if shutil.which("g++") is None:
+        pytest.skip("no compiler")
+    try:
+        exe = _build("xsgrep_double_tsan", ["-O1", "-g", "-fsanitize=thread"])
+    except subprocess.CalledProcessError:
+        pytest.skip("ThreadSanitizer runtime not available")
+    probe = subprocess.run([exe, "--selftest-host"], capture_output=True, text=True)
+    if probe.returncode != 0 and "ThreadSanitizer" not in probe.stderr:
+        pytest.skip("ThreadSanitizer binaries do not run here: " + probe.stderr[-200:])
+    return exe
+
+
+@pytest.fixture(scope="module")
+def double_asan():
+    try:
+        exe = _build("xsgrep_double_asan", ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"])
+    except subprocess.CalledProcessError:
+        pytest.skip("AddressSanitizer runtime not available")
+    probe = subprocess.run([exe, "--selftest-host"], capture_output=True, text=True)
+    if probe.returncode != 0 and "Sanitizer" not in probe.stderr:
+        pytest.skip("sanitizer binaries do not run here: " + probe.stderr[-200:])
+    return exe
+
+
+def test_double_is_not_the_product():
+    """The double must stay test infrastructure: nothing outside tests/ names it, and the product driver links libxsg.so."""
+    for base in ("xsearch_b200", "include", "bench.py", "__graft_entry__.py", "tools"):
+        path = os.path.join(ROOT, base)
+        files = [path] if os.path.isfile(path) else [os.path.join(d, f) for d, _, fs in os.walk(path) for f in fs
+                                                     if f.endswith((".py", ".cpp", ".hpp", ".h", ".cu", ".cuh", ".inc", ".sh")) or f == "Makefile"]
+        for f in files:
+            text = open(f, errors="replace").read()
+            assert "testdouble" not in text and "xsgrep_double" not in text, f
+    assert "-lxsg" in open(os.path.join(ROOT, "xsearch_b200", "cpp", "Makefile")).read()
+
+
+def test_all_tags(double, tmp_path):
+    capi.check_all_tags(double, tmp_path)
+
+
+def test_with_meta_file(double, tmp_path):
+    capi.check_with_meta_file(double, tmp_path)
+
+
+def test_edge_files(double, tmp_path):
+    capi.check_edge_files(double, tmp_path)
+
+
+def test_ignore_case(double, tmp_path):
+    capi.check_ignore_case(double, tmp_path)
+
+
+def test_errors(double, tmp_path):
+    capi.check_errors(double, tmp_path)
+
+
+def test_regex(double, tmp_path):
+    golden = rx.json.load(open(os.path.join(rx.GOLD, "regex_vectors.json")))
+    rx.check_extern_search_regex(golden, rx.corpora(), double, tmp_path)
+
+
+def _ragged_text(rng, n_lines):
+    """Lines of wildly different lengths (0 .. 200 kB) so that chunk ends, segment ends and slice ends fall everywhere."""
+    words = [b"needle", b"nneedle", b"need", b"le", b"x", b"hay stack", b""]
+    lines = []
+    for _ in range(n_lines):
+        r = rng.random()
+        if r < 0.02:
+            body = b"y" * int(rng.integers(50000, 200000)) + (b"needle" if rng.random() < 0.5 else b"")
+        else:
+            body = b" ".join(words[int(i)] for i in rng.integers(0, len(words), int(rng.integers(0, 12))))
+        lines.append(body)
+    return np.frombuffer(b"\n".join(lines) + (b"\n" if rng.random() < 0.5 else b""), dtype=np.uint8).copy()
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_geometry(double, tmp_path, seed):
+    """Random files x random (min_chunk, segment, readers): carries of every length, segments that hold no complete
+    chunk, one-off buffers, an unterminated last line -- every tag equals the oracle on the same chunk table."""
+    oracle, _ = oracle_lib.load(build=False)
+    rng = np.random.default_rng(seed)
+    buf = _ragged_text(rng, 4000)
+    path = tmp_path / "ragged.txt"
+    buf.tofile(path)
+    for _ in range(4):
+        min_chunk = int(rng.choice([4096, 20000, 65536, 300000]))
+        seg = int(min_chunk * rng.choice([2, 3, 7]))
+        readers = int(rng.integers(1, 5))
+        bounds = oracle.chunk_bounds(buf, min_chunk)
+        extra = ["--min-chunk", str(min_chunk), "--segment-bytes", str(seg), "--readers", str(readers)]
+        for tag in capi.TAGS:
+            live = ["--live"] if rng.random() < 0.5 else []
+            exp = capi.expected_output(oracle, buf, b"needle", bounds, tag)
+            assert capi.run_xsgrep(double, tag, b"needle", path, extra + live) == exp, (seed, min_chunk, seg, readers, tag)
+
+
+def test_injected_failure_closes_the_result(double, tmp_path):
+    """A failing push (XSG_DOUBLE_FAIL_PUSH) must end the search: exit code 2 with the library's message, results of
+    the segments before it still delivered in order, no hang -- joined and live, one and several readers."""
+    oracle, _ = oracle_lib.load(build=False)
+    buf = _ragged_text(np.random.default_rng(9), 3000)
+    path = tmp_path / "f.txt"
+    buf.tofile(path)
+    full = capi.expected_output(oracle, buf, b"needle", oracle.chunk_bounds(buf, 20000), "match_byte_offsets")
+    for fail_at in (0, 1, 5):
+        for extra in ([], ["--live", "--readers", "3"]):
+            env = dict(os.environ, XSG_DOUBLE_FAIL_PUSH=str(fail_at))
+            out = subprocess.run([double, "--tag", "match_byte_offsets", "--min-chunk", "20000", "--segment-bytes", "40000",
+                                  *extra, "needle", str(path)], capture_output=True, text=True, env=env, timeout=60)
+            assert out.returncode == 2, (fail_at, extra, out.stderr)
+            assert "injected failure of push %d" % fail_at in out.stderr
+            assert full.startswith(out.stdout) and len(out.stdout) < len(full), (fail_at, extra)
+            if fail_at == 0:
+                assert out.stdout == ""
+
+
+def test_thread_sanitizer(double_tsan, tmp_path):
+    """Readers, pusher, verification threads and a live consumer under ThreadSanitizer: no report, same output."""
+    oracle, _ = oracle_lib.load(build=False)
+    buf = _ragged_text(np.random.default_rng(5), 1500)
+    path = tmp_path / "t.txt"
+    buf.tofile(path)
+    bounds = oracle.chunk_bounds(buf, 20000)
+    env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 exitcode=66")
+    base = ["--min-chunk", "20000", "--segment-bytes", "60000", "--readers", "4", "-j", "4"]
+    for tag in ("count", "lines", "line_indices"):
+        for live in ([], ["--live"]):
+            out = subprocess.run([double_tsan, "--tag", tag, *base, *live, "needle", str(path)], capture_output=True,
+                                 env=env, timeout=300)
+            assert out.returncode == 0 and b"ThreadSanitizer" not in out.stderr, out.stderr.decode()[-2000:]
+            assert out.stdout.decode("latin-1") == capi.expected_output(oracle, buf, b"needle", bounds, tag), (tag, live)
+    # regex mode: candidate verification on four threads with per-thread DFA caches
+    out = subprocess.run([double_tsan, "-E", "--tag", "count_lines", *base, "--live", "ne+d(le|y)", str(path)],
+                         capture_output=True, env=env, timeout=300)
+    assert out.returncode == 0 and b"ThreadSanitizer" not in out.stderr, out.stderr.decode()[-2000:]
+    import re
+    lines = buf.tobytes().split(b"\n")
+    assert int(out.stdout) == sum(1 for line in lines if re.search(rb"ne+d(le|y)", line))
+
+
+def test_address_sanitizer(double_asan, tmp_path):
+    """The carry arithmetic (headroom copies, one-off buffers, string building from recycled buffers) under
+    AddressSanitizer + UBSan: the edge files, a meta-file run and a regular expression, no report."""
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=1:abort_on_error=0:exitcode=67")
+
+    def run(args, **kw):
+        out = subprocess.run(args, capture_output=True, env=env, timeout=300, **kw)
+        assert b"Sanitizer" not in out.stderr and b"runtime error" not in out.stderr, out.stderr.decode()[-3000:]
+        return out
+
+    real_run = subprocess.run
+    try:
+        def checked_run(args, *a, **kw):
+            kw.setdefault("env", env)
+            out = real_run(args, *a, **kw)
+            err = out.stderr if isinstance(out.stderr, str) else (out.stderr or b"").decode("latin-1")
+            assert "Sanitizer" not in err and "runtime error" not in err, err[-3000:]
+            return out
+        subprocess.run = checked_run
+        capi.check_edge_files(double_asan, tmp_path)
+        capi.check_with_meta_file(double_asan, tmp_path)
+        capi.check_errors(double_asan, tmp_path)
+    finally:
+        subprocess.run = real_run
+    buf = _ragged_text(np.random.default_rng(6), 1500)
+    path = tmp_path / "a.txt"
+    buf.tofile(path)
+    for tag in ("lines", "match_byte_offsets"):
+        out = run([double_asan, "-E", "--tag", tag, "--min-chunk", "20000", "--segment-bytes", "60000", "--readers", "3",
+                   "-j", "3", "--live", "n+e{2}dle|stack", str(path)])
+        assert out.returncode == 0, out.stderr.decode()[-2000:]
+    env_fail = dict(env, XSG_DOUBLE_FAIL_PUSH="2")
+    out = subprocess.run([double_asan, "--tag", "lines", "--min-chunk", "20000", "--segment-bytes", "40000", "--readers", "3",
+                          "needle", str(path)], capture_output=True, env=env_fail, timeout=300)
+    assert out.returncode == 2 and b"Sanitizer" not in out.stderr, out.stderr.decode()[-3000:]
