@@ -197,38 +197,22 @@ def test_thread_sanitizer(double_tsan, tmp_path):
     assert int(out.stdout) == sum(1 for line in lines if re.search(rb"ne+d(le|y)", line))
 
 
-def test_address_sanitizer(double_asan, tmp_path):
+def test_address_sanitizer(double_asan, tmp_path, monkeypatch):
     """The carry arithmetic (headroom copies, one-off buffers, string building from recycled buffers) under
-    AddressSanitizer + UBSan: the edge files, a meta-file run and a regular expression, no report."""
-    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=1:abort_on_error=0:exitcode=67")
-
-    def run(args, **kw):
-        out = subprocess.run(args, capture_output=True, env=env, timeout=300, **kw)
-        assert b"Sanitizer" not in out.stderr and b"runtime error" not in out.stderr, out.stderr.decode()[-3000:]
-        return out
-
-    real_run = subprocess.run
-    try:
-        def checked_run(args, *a, **kw):
-            kw.setdefault("env", env)
-            out = real_run(args, *a, **kw)
-            err = out.stderr if isinstance(out.stderr, str) else (out.stderr or b"").decode("latin-1")
-            assert "Sanitizer" not in err and "runtime error" not in err, err[-3000:]
-            return out
-        subprocess.run = checked_run
-        capi.check_edge_files(double_asan, tmp_path)
-        capi.check_with_meta_file(double_asan, tmp_path)
-        capi.check_errors(double_asan, tmp_path)
-    finally:
-        subprocess.run = real_run
+    AddressSanitizer + UBSan with leak checking: the edge files, a meta-file run, a regular expression and the failure
+    path.  A report makes the binary exit with 67 (UBSan aborts), which the check functions see as a failed run."""
+    monkeypatch.setenv("ASAN_OPTIONS", "detect_leaks=1:exitcode=67")
+    capi.check_edge_files(double_asan, tmp_path)
+    capi.check_with_meta_file(double_asan, tmp_path)
+    capi.check_errors(double_asan, tmp_path)
     buf = _ragged_text(np.random.default_rng(6), 1500)
     path = tmp_path / "a.txt"
     buf.tofile(path)
     for tag in ("lines", "match_byte_offsets"):
-        out = run([double_asan, "-E", "--tag", tag, "--min-chunk", "20000", "--segment-bytes", "60000", "--readers", "3",
-                   "-j", "3", "--live", "n+e{2}dle|stack", str(path)])
-        assert out.returncode == 0, out.stderr.decode()[-2000:]
-    env_fail = dict(env, XSG_DOUBLE_FAIL_PUSH="2")
+        out = subprocess.run([double_asan, "-E", "--tag", tag, "--min-chunk", "20000", "--segment-bytes", "60000", "--readers", "3",
+                              "-j", "3", "--live", "n+e{2}dle|stack", str(path)], capture_output=True, timeout=300)
+        assert out.returncode == 0 and b"Sanitizer" not in out.stderr, out.stderr.decode()[-3000:]
+    monkeypatch.setenv("XSG_DOUBLE_FAIL_PUSH", "2")
     out = subprocess.run([double_asan, "--tag", "lines", "--min-chunk", "20000", "--segment-bytes", "40000", "--readers", "3",
-                          "needle", str(path)], capture_output=True, env=env_fail, timeout=300)
+                          "needle", str(path)], capture_output=True, timeout=300)
     assert out.returncode == 2 and b"Sanitizer" not in out.stderr, out.stderr.decode()[-3000:]
