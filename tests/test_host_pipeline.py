@@ -146,7 +146,8 @@ def test_random_geometry(double, tmp_path, seed):
         seg = int(min_chunk * rng.choice([2, 3, 7]))
         readers = int(rng.integers(1, 5))
         bounds = oracle.chunk_bounds(buf, min_chunk)
-        extra = ["--min-chunk", str(min_chunk), "--segment-bytes", str(seg), "--readers", str(readers)]
+        extra = ["--min-chunk", str(min_chunk), "--segment-bytes", str(seg), "--readers", str(readers),
+                 "--reader", str(rng.choice(["pread", "mmap"]))]
         for tag in capi.TAGS:
             live = ["--live"] if rng.random() < 0.5 else []
             exp = capi.expected_output(oracle, buf, b"needle", bounds, tag)
@@ -183,7 +184,7 @@ def test_thread_sanitizer(double_tsan, tmp_path):
     env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 exitcode=66")
     base = ["--min-chunk", "20000", "--segment-bytes", "60000", "--readers", "4", "-j", "4"]
     for tag in ("count", "lines", "line_indices"):
-        for live in ([], ["--live"]):
+        for live in ([], ["--live"], ["--live", "--reader", "mmap"]):
             out = subprocess.run([double_tsan, "--tag", tag, *base, *live, "needle", str(path)], capture_output=True,
                                  env=env, timeout=300)
             assert out.returncode == 0 and b"ThreadSanitizer" not in out.stderr, out.stderr.decode()[-2000:]
@@ -205,6 +206,10 @@ def test_address_sanitizer(double_asan, tmp_path, monkeypatch):
     capi.check_edge_files(double_asan, tmp_path)
     capi.check_with_meta_file(double_asan, tmp_path)
     capi.check_errors(double_asan, tmp_path)
+    for name in ("empty", "no_trailing_newline", "long_line"):  # files written by check_edge_files
+        out = subprocess.run([double_asan, "--tag", "lines", "--reader", "mmap", "--min-chunk", "65536", "--segment-bytes",
+                              "262144", "--readers", "3", "needle", str(tmp_path / (name + ".txt"))], capture_output=True, timeout=300)
+        assert out.returncode == 0 and b"Sanitizer" not in out.stderr, out.stderr.decode()[-3000:]
     buf = _ragged_text(np.random.default_rng(6), 1500)
     path = tmp_path / "a.txt"
     buf.tofile(path)

@@ -2,7 +2,8 @@
 // example/grep.cpp:66-80 and checkit.cpp).  Also the driver of the C++ API tests (tests/test_cpp_api.py).
 //
 //   xsgrep [--tag lines|count|count_lines|match_byte_offsets|line_byte_offsets|line_indices] [--meta FILE]
-//          [-j N] [--readers N] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D] [--live] [-i] [-E | -F]
+//          [-j N] [--readers N] [--reader pread|mmap] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D] [--live]
+//          [-i] [-E | -F]
 //          PATTERN FILE
 //   -E / -F read PATTERN as a regular expression / as plain text; default: the reference's rule (utils.h:17-24).
 //   A regular expression is searched by scanning for its required literals on the GPU and running the expression
@@ -201,7 +202,14 @@ int main(int argc, char** argv) {
     else if (s == "--min-chunk") a.opt.min_chunk = std::strtoull(next().c_str(), nullptr, 10);
     else if (s == "--segment-bytes") a.opt.segment_bytes = std::strtoull(next().c_str(), nullptr, 10);
     else if (s == "--device") a.opt.device = std::atoi(next().c_str());
-    else if (s == "--live") a.live = true;
+    else if (s == "--reader") {
+      const std::string m = next();
+      if (m != "pread" && m != "mmap") {
+        std::fprintf(stderr, "xsgrep: --reader pread|mmap\n");
+        return 64;
+      }
+      a.opt.reader_mode = m == "mmap" ? xs::Options::ReaderMode::MMAP : xs::Options::ReaderMode::PREAD;
+    } else if (s == "--live") a.live = true;
     else if (s == "-i" || s == "--ignore-case") a.opt.ignore_case = true;
     else pos.push_back(s);
   }
