@@ -35,18 +35,20 @@ HEADERS = [os.path.join(ROOT, "include", "xsg.h"), os.path.join(ROOT, "oracle", 
           [os.path.join(ROOT, "include", "xsearch_b200", f) for f in sorted(os.listdir(os.path.join(ROOT, "include", "xsearch_b200")))]
 
 
-def _build(name, flags):
-    """xsgrep.cpp + the test double + the oracle's C restatement in one executable (no libxsg.so involved)."""
+def _build(name, flags, main_src=None):
+    """xsgrep.cpp (or another program on xsearch.hpp) + the test double + the oracle's C restatement in one executable
+    (no libxsg.so involved)."""
     os.makedirs(OUT, exist_ok=True)
     exe = os.path.join(OUT, name)
-    newest = max(os.path.getmtime(p) for p in SOURCES + HEADERS)
+    sources = SOURCES if main_src is None else [main_src, SOURCES[1]]
+    newest = max(os.path.getmtime(p) for p in sources + HEADERS)
     if os.path.exists(exe) and os.path.getmtime(exe) >= newest:
         return exe
     obj = os.path.join(OUT, name + ".oracle.o")
     subprocess.check_call(["gcc", "-O2", "-c", *[f for f in flags if f.startswith("-fsanitize") or f == "-g"],
                            "-o", obj, os.path.join(ROOT, "oracle", "xs_oracle.c")])
     subprocess.check_call(["g++", "-std=c++20", "-Wall", "-Wextra", "-pthread", *flags, "-I" + os.path.join(ROOT, "include"),
-                           "-o", exe, *SOURCES, obj])
+                           "-o", exe, *sources, obj])
     return exe
 
 
@@ -116,6 +118,43 @@ def test_errors(double, tmp_path):
 def test_regex(double, tmp_path):
     golden = rx.json.load(open(os.path.join(rx.GOLD, "regex_vectors.json")))
     rx.check_extern_search_regex(golden, rx.corpora(), double, tmp_path)
+
+
+def test_reference_call_shapes(tmp_path):
+    """tests/cpp/reference_usage.cpp: every call shape the reference's README, examples and tests use (overloads, a
+    char* meta path, join + size, copyResultSafe, live loops, running totals, an ignored searcher) compiles against
+    xsearch.hpp and returns what the oracle says."""
+    exe = _build("reference_usage", ["-O2"], os.path.join(CPP, "reference_usage.cpp"))
+    oracle, _ = oracle_lib.load(build=False)
+    rng = np.random.default_rng(12)
+    words = [b"Needle", b"needle", b"NEEDLE", b"nneedle", b"hay", b"stack of", b""]
+    buf = np.frombuffer(b"\n".join(b" ".join(words[int(i)] for i in rng.integers(0, len(words), int(rng.integers(0, 9))))
+                                   for _ in range(60000)) + b"\n", dtype=np.uint8).copy()
+    path, meta = tmp_path / "u.txt", tmp_path / "u.meta"
+    buf.tofile(path)
+    mb = oracle.chunk_bounds(buf, 65536)
+    capi.write_meta(meta, mb)
+    one = np.array([buf.size], dtype=np.uint64)
+    low = oracle.to_lower(buf)
+    pat = b"needle"
+    out = subprocess.run([exe, pat.decode(), str(path), str(meta)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    got = dict(line.split(" ", 1) for line in out.stdout.splitlines())
+    st, ln = oracle.lines(buf, pat, one)
+    assert got["S1"] == "%d %d" % (len(st), int(ln.sum()))
+    assert got["S2"] == "%d" % len(oracle.lines(buf, pat, mb)[0])
+    assert got["S3"] == "%d" % oracle.count(buf, pat, mb, False)
+    assert got["S4"] == "%d" % oracle.count(buf, pat, one, False)
+    assert got["S4i"] == "%d" % oracle.count(low, pat, one, True)
+    assert got["S5"] == "%d" % oracle.count(low, pat, mb, False)
+    lbo = oracle.line_byte_offsets(buf, pat, one)
+    assert got["S6"] == "%d %d 1" % (len(lbo), int(lbo.sum()))
+    li = oracle.line_indices(buf, pat, mb)
+    assert got["S6i"] == "%d %d" % (len(li), int(li.sum()))
+    assert got["S6m"] == "%d" % len(oracle.match_byte_offsets(buf, pat, one))
+    assert got["S7"] == "%d 1 1" % oracle.count(buf, pat, one, False)
+    assert got["S8"] == "ok"
+    assert int(got["S5"]) > int(got["S3"]) > 0  # ignore case finds more: the corpus is not trivial
 
 
 def _ragged_text(rng, n_lines):
