@@ -28,5 +28,12 @@ for tag in count lines; do
     done
   done
 done
+# reader mode A/B (xs::Options::reader_mode): memcpy out of a mapping instead of pread, DESIGN.md 8
+for mode in pread mmap; do
+  for r in 1 4 8 12; do
+    ./xsearch_b200/cpp/xsgrep --tag count --readers $r --reader $mode Sherlock $F 2>> $O.err > /dev/null
+    echo "tag=count reader=$mode readers=$r | $(tail -1 $O.err)" >> $O
+  done
+done
 rm -f $F
 cat $O
