@@ -103,8 +103,12 @@ struct Options {
 };
 
 // ---- result collector ------------------------------------------------------------------------------
-// Flat, ordered collection of result elements with the reference's blocking-iterator behaviour.
+// Ordered collection of result elements with the reference's blocking-iterator behaviour.
 // For count tags the elements are running totals and size() is the total.
+// Elements are kept as the PARTS they arrive in (one per scanned segment, moved in, never touched again): adding a
+// part is O(1) whatever its size, and the iterator takes the lock once per part, not per element -- a dense search
+// delivers 10^8 offsets per 10 GB, and a lock round trip per element would cost seconds where the scan costs
+// milliseconds.
 template <class T>
 class Result {
  public:
@@ -112,24 +116,32 @@ class Result {
    public:
     explicit iterator(Result* r) : _r(r) {}
     iterator& operator++() {
-      ++_i;
+      ++_k;
       return *this;
     }
+    // valid after operator!= returned true (what a range-for does); blocks like operator!= otherwise
     const T& operator*() const {
-      std::unique_lock lock(_r->_m);
-      return _r->_data[_i];
+      if (_k >= _n) fetch();
+      return _cur[_k];
     }
-    // blocks until element _i exists or the result is closed (ResultTypes.h:48-60)
-    bool operator!=(const iterator&) const {
-      std::unique_lock lock(_r->_m);
-      _r->_cv.wait(lock, [&] { return _i < _r->_data.size() || _r->_closed; });
-      return _i < _r->_data.size();
-    }
+    // blocks until the next element exists or the result is closed (ResultTypes.h:48-60)
+    bool operator!=(const iterator&) const { return _k < _n || fetch(); }
     bool operator==(const iterator& o) const { return !(*this != o); }
 
    private:
+    bool fetch() const {  // next part (parts are never empty); false: closed and nothing left
+      std::unique_lock lock(_r->_m);
+      _r->_cv.wait(lock, [&] { return _next < _r->_parts.size() || _r->_closed; });
+      if (_next >= _r->_parts.size()) return false;
+      const std::vector<T>& p = _r->_parts[_next++];
+      _cur = p.data();
+      _n = p.size();
+      _k = 0;
+      return true;
+    }
     Result* _r;
-    size_t _i = 0;
+    mutable const T* _cur = nullptr;  // the part being walked: immutable once added, read without the lock
+    mutable size_t _n = 0, _k = 0, _next = 0;
   };
 
   explicit Result(bool counting) : _counting(counting) {}
@@ -140,7 +152,10 @@ class Result {
   bool add(std::vector<T>&& part) {
     std::unique_lock lock(_m);
     if (_closed) return false;
-    for (auto& v : part) _data.push_back(std::move(v));
+    if (part.empty()) return true;
+    _starts.push_back(_count);
+    _count += part.size();
+    _parts.push_back(std::move(part));
     _cv.notify_all();
     return true;
   }
@@ -157,9 +172,9 @@ class Result {
   size_t size() const {
     std::unique_lock lock(_m);
     if constexpr (std::is_same_v<T, uint64_t>) {
-      if (_counting) return _data.empty() ? 0 : static_cast<size_t>(_data.back());
+      if (_counting) return _parts.empty() ? 0 : static_cast<size_t>(_parts.back().back());
     }
-    return _data.size();
+    return _count;
   }
   bool empty() const { return size() == 0; }
   bool is_closed() const {
@@ -172,11 +187,16 @@ class Result {
   }
   std::vector<T> copyResultSafe() const {
     std::unique_lock lock(_m);
-    return std::vector<T>(_data.begin(), _data.end());
+    std::vector<T> out;
+    out.reserve(_count);
+    for (const std::vector<T>& p : _parts) out.insert(out.end(), p.begin(), p.end());
+    return out;
   }
   T at(size_t i) const {
     std::unique_lock lock(_m);
-    return _data.at(i);
+    if (i >= _count) throw std::out_of_range("xs::Result::at");
+    const size_t part = static_cast<size_t>(std::upper_bound(_starts.begin(), _starts.end(), i) - _starts.begin()) - 1;
+    return _parts[part][i - _starts[part]];
   }
   T operator[](size_t i) const { return at(i); }
   iterator begin() { return iterator(this); }
@@ -186,7 +206,9 @@ class Result {
   const bool _counting;
   mutable std::mutex _m;
   mutable std::condition_variable _cv;
-  std::deque<T> _data;  // deque: references handed out by the iterator survive later push_backs
+  std::deque<std::vector<T>> _parts;  // deque: a part handed to an iterator stays where it is when later parts arrive
+  std::vector<size_t> _starts;        // index of the first element of every part
+  size_t _count = 0;
   bool _closed = false;
 };
 

@@ -98,6 +98,29 @@ int selftest_host() {
   prod.join();
   if (expect != 15 || r.size() != 15 || !r.is_closed() || r.add({1})) return 1;
   if (r.copyResultSafe().size() != 15 || r.at(7) != 7) return 1;
+  // parts of different sizes (also empty ones): indexing crosses part edges, every begin() starts at the front
+  xs::Result<uint64_t> q(false);
+  q.add({});
+  q.add({0});
+  q.add({1, 2, 3});
+  q.add({});
+  q.add({4, 5});
+  if (q.size() != 6) return 1;
+  for (uint64_t i = 0; i < 6; ++i)
+    if (q.at(i) != i || q[i] != i) return 1;
+  try {
+    q.at(6);
+    return 1;
+  } catch (const std::out_of_range&) {
+  }
+  q.close();
+  for (int pass = 0; pass < 2; ++pass) {
+    uint64_t n = 0;
+    for (auto it = q.begin(); it != q.end(); ++it, ++n)
+      if (*it != n) return 1;
+    if (n != 6) return 1;
+  }
+  if (q.copyResultSafe() != std::vector<uint64_t>{0, 1, 2, 3, 4, 5}) return 1;
   // count tags: elements are running totals, size() is the total
   xs::Result<uint64_t> c(true);
   c.add({4});
