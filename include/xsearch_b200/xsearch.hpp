@@ -536,10 +536,21 @@ class Searcher {
       if (n && (xsg_result_part_copy(res, part, XSG_LINES, st.data(), n) != XSG_OK ||
                 xsg_result_part_copy_line_lengths(res, part, ln.data(), n) != XSG_OK))
         return false;
-      typename ResultT::part_type out;
-      out.reserve(n);
-      for (uint64_t i = 0; i < n; ++i)
-        out.emplace_back(reinterpret_cast<const char*>(seg.ptr) + (st[i] - seg.goff), static_cast<size_t>(ln[i]));
+      // one std::string per matching line (as in the reference, search_wrappers.h:187-207) is one allocation per
+      // line: the work num_threads is for on this path
+      typename ResultT::part_type out(n);
+      const char* base = reinterpret_cast<const char*>(seg.ptr) - seg.goff;
+      auto build = [&](uint64_t lo, uint64_t hi) {
+        for (uint64_t i = lo; i < hi; ++i) out[i].assign(base + st[i], static_cast<size_t>(ln[i]));
+      };
+      const uint64_t nt = std::min<uint64_t>(static_cast<uint64_t>(_num_threads), n / 16384 + 1);
+      if (nt <= 1) {
+        build(0, n);
+      } else {
+        std::vector<std::thread> pool;
+        for (uint64_t t = 0; t < nt; ++t) pool.emplace_back(build, n * t / nt, n * (t + 1) / nt);
+        for (auto& t : pool) t.join();
+      }
       _result.add(std::move(out));
     }
     return true;
