@@ -228,6 +228,14 @@ def test_thread_sanitizer(double_tsan, tmp_path):
                                  env=env, timeout=300)
             assert out.returncode == 0 and b"ThreadSanitizer" not in out.stderr, out.stderr.decode()[-2000:]
             assert out.stdout.decode("latin-1") == capi.expected_output(oracle, buf, b"needle", bounds, tag), (tag, live)
+    # parts of more than 16 k matching lines: their strings are built on -j threads
+    dense = np.frombuffer(b"".join(b"needle %d\n" % i for i in range(120000)), dtype=np.uint8).copy()
+    dpath = tmp_path / "dense.txt"
+    dense.tofile(dpath)
+    out = subprocess.run([double_tsan, "--tag", "lines", "--min-chunk", "400000", "--segment-bytes", "800000", "--readers", "2",
+                          "-j", "4", "--live", "needle", str(dpath)], capture_output=True, env=env, timeout=300)
+    assert out.returncode == 0 and b"ThreadSanitizer" not in out.stderr, out.stderr.decode()[-2000:]
+    assert out.stdout == dense.tobytes()
     # regex mode: candidate verification on four threads with per-thread DFA caches
     out = subprocess.run([double_tsan, "-E", "--tag", "count_lines", *base, "--live", "ne+d(le|y)", str(path)],
                          capture_output=True, env=env, timeout=300)
