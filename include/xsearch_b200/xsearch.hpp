@@ -539,9 +539,9 @@ class Searcher {
       // one std::string per matching line (as in the reference, search_wrappers.h:187-207) is one allocation per
       // line: the work num_threads is for on this path
       typename ResultT::part_type out(n);
-      const char* base = reinterpret_cast<const char*>(seg.ptr) - seg.goff;
+      const char* base = reinterpret_cast<const char*>(seg.ptr);
       auto build = [&](uint64_t lo, uint64_t hi) {
-        for (uint64_t i = lo; i < hi; ++i) out[i].assign(base + st[i], static_cast<size_t>(ln[i]));
+        for (uint64_t i = lo; i < hi; ++i) out[i].assign(base + (st[i] - seg.goff), static_cast<size_t>(ln[i]));
       };
       const uint64_t nt = std::min<uint64_t>(static_cast<uint64_t>(_num_threads), n / 16384 + 1);
       if (nt <= 1) {
