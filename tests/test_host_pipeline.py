@@ -243,6 +243,11 @@ def test_thread_sanitizer(double_tsan, tmp_path):
     import re
     lines = buf.tobytes().split(b"\n")
     assert int(out.stdout) == sum(1 for line in lines if re.search(rb"ne+d(le|y)", line))
+    # match-level kinds run the Pike VM (thread-local scratch) instead of the per-thread DFA
+    out = subprocess.run([double_tsan, "-E", "--tag", "count", *base, "ne+d(le|y)", str(path)], capture_output=True, env=env,
+                         timeout=300)
+    assert out.returncode == 0 and b"ThreadSanitizer" not in out.stderr, out.stderr.decode()[-2000:]
+    assert int(out.stdout) == sum(len(re.findall(rb"ne+d(le|y)", line)) for line in lines)
 
 
 def test_address_sanitizer(double_asan, tmp_path, monkeypatch):
