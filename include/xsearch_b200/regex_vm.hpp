@@ -642,19 +642,22 @@ inline bool Program::search(const char* text, size_t n, size_t from, Span* out) 
 // existence does not depend on priorities: the set of program counters alive after each byte is a DFA state.  States
 // and transitions are built on first use (the classic lazy subset construction, as in re2's DFA), one table row of
 // 256 entries per state, at most kMaxStates states (then the cache is flushed).  Not thread-safe: one Dfa per
-// verification thread; the Program is shared.  Programs with assertions are answered by the Pike VM.
+// verification thread; the Program is shared.
+//
+// Assertions (^ $ \b \B) look at the neighbours of a position, so a program that holds some runs a second form of
+// the same construction (as re2's DFA does with its "needs flags" states): closure() STOPS at an assertion and keeps
+// it in the state as pending; the state also carries what lies before the position (FLAG_START: nothing, FLAG_WORD:
+// a word byte).  A transition on byte c first resolves the pending assertions with c as the byte behind the position
+// (expand()), then consumes c; the end of the line resolves them once more with "nothing behind".  States without
+// pending assertions do not depend on the flags and are stored with flags 0, so a program whose start holds no
+// assertion keeps ONE start state and the first-byte skip.
 class Dfa {
  public:
-  explicit Dfa(const Program& p) : _p(p), _usable(!p.has_assertions()) {
-    if (_usable) reset();
-  }
+  explicit Dfa(const Program& p) : _p(p), _assert(p.has_assertions()) { reset(); }
 
   bool matches(const char* text, size_t n) {
-    if (!_usable) {
-      Span m;
-      return _p.search(text, n, 0, &m);
-    }
     const unsigned char* s = reinterpret_cast<const unsigned char*>(text);
+    if (_assert) return matches_assert(s, n);
     int32_t st = _start;
     if (_accept[size_t(st)]) return true;
     for (size_t i = 0; i < n; ++i) {
@@ -675,10 +678,13 @@ class Dfa {
  private:
   static constexpr size_t kMaxStates = 2048;
   static constexpr int32_t kAcceptBit = 1 << 30;
+  static constexpr uint8_t FLAG_WORD = 1, FLAG_START = 2;
 
   void reset() {
     _sets.clear();
     _accept.clear();
+    _flags.clear();
+    _eot.clear();
     _next.clear();
     _index.clear();
     _mark.assign(_p._prog.size(), 0);
@@ -687,7 +693,95 @@ class Dfa {
     bool acc = false;
     begin_set();
     closure(0, &set, &acc);
-    _start = intern(std::move(set), acc);
+    _start = intern(std::move(set), acc, FLAG_START);
+  }
+
+  static bool is_assertion(const Inst& i) {
+    return i.op == Inst::BOL || i.op == Inst::EOL || i.op == Inst::WORDB || i.op == Inst::NWORDB;
+  }
+
+  // ---- programs with assertions ----------------------------------------------------------------------------
+  bool matches_assert(const unsigned char* s, size_t n) {
+    int32_t st = _start;
+    if (_accept[size_t(st)]) return true;
+    for (size_t i = 0; i < n; ++i) {
+      if (st == _start && _p._has_first) {  // the start state holds no assertion then: flags 0, one state
+        while (i < n && !_p._first[s[i]]) ++i;
+        if (i >= n) break;
+      }
+      int32_t nx = _next[size_t(st) * 256 + s[i]];
+      if (nx < 0) nx = step_assert(st, s[i]);
+      if (nx & kAcceptBit) return true;
+      st = nx;
+    }
+    if (_eot[size_t(st)] < 0) {  // pending assertions against the end of the line
+      _cons.clear();
+      _eot[size_t(st)] = expand(st, /*eot=*/true, 0) ? 1 : 0;
+    }
+    return _eot[size_t(st)] != 0;
+  }
+
+  // Resolves the pending assertions of state st at its position, `c` being the byte behind it (eot: none).  The
+  // consuming instructions alive there are left in _cons; true when MATCH is reached.
+  bool expand(int32_t st, bool eot, unsigned char c) {
+    const uint8_t flags = _flags[size_t(st)];
+    const bool before = (flags & FLAG_WORD) != 0, after = !eot && is_word(c);
+    bool acc = false;
+    begin_set();
+    _stack.clear();
+    const std::vector<uint32_t>& set = _sets[size_t(st)];
+    for (size_t k = set.size(); k-- > 0;) _stack.push_back(set[k]);
+    while (!_stack.empty()) {
+      const uint32_t pc = _stack.back();
+      _stack.pop_back();
+      if (_mark[pc] == _epoch) continue;
+      _mark[pc] = _epoch;
+      const Inst& i = _p._prog[pc];
+      switch (i.op) {
+        case Inst::JMP: _stack.push_back(i.x); break;
+        case Inst::SPLIT: _stack.push_back(i.y), _stack.push_back(i.x); break;
+        case Inst::MATCH: acc = true; break;
+        case Inst::BOL:
+          if (flags & FLAG_START) _stack.push_back(pc + 1);
+          break;
+        case Inst::EOL:
+          if (eot) _stack.push_back(pc + 1);
+          break;
+        case Inst::WORDB:
+        case Inst::NWORDB:
+          if ((before != after) == (i.op == Inst::WORDB)) _stack.push_back(pc + 1);
+          break;
+        default: _cons.push_back(pc); break;  // BYTE, SET
+      }
+    }
+    return acc;
+  }
+
+  int32_t step_assert(int32_t st, unsigned char c) {
+    _cons.clear();
+    if (expand(st, /*eot=*/false, c)) {  // a match ends at this position: the search is over
+      _next[size_t(st) * 256 + c] = kAcceptBit;
+      return kAcceptBit;
+    }
+    std::vector<uint32_t> set;
+    bool acc = false;
+    begin_set();
+    for (uint32_t pc : _cons) {
+      const Inst& i = _p._prog[pc];
+      if ((i.op == Inst::BYTE && i.byte == c) || (i.op == Inst::SET && _p._sets[i.x].has(c))) closure(pc + 1, &set, &acc);
+    }
+    closure(0, &set, &acc);  // a match may start at the next byte as well
+    if (_sets.size() >= kMaxStates) {
+      std::vector<uint32_t> cur = _sets[size_t(st)];
+      const bool cur_acc = _accept[size_t(st)] != 0;
+      const uint8_t cur_flags = _flags[size_t(st)];
+      reset();
+      st = intern(std::move(cur), cur_acc, cur_flags);
+    }
+    int32_t nx = intern(std::move(set), acc, is_word(c) ? FLAG_WORD : 0);
+    if (acc) nx |= kAcceptBit;
+    _next[size_t(st) * 256 + c] = nx;
+    return nx;
   }
 
   void begin_set() {
@@ -711,20 +805,26 @@ class Dfa {
         case Inst::JMP: _stack.push_back(i.x); break;
         case Inst::SPLIT: _stack.push_back(i.y), _stack.push_back(i.x); break;
         case Inst::MATCH: *acc = true; break;
-        default: set->push_back(pc); break;  // BYTE, SET (no assertions in a usable program)
+        default: set->push_back(pc); break;  // BYTE, SET; an assertion stays pending in the state (see expand)
       }
     }
   }
 
-  int32_t intern(std::vector<uint32_t>&& set, bool acc) {
+  int32_t intern(std::vector<uint32_t>&& set, bool acc, uint8_t flags = 0) {
     std::sort(set.begin(), set.end());
+    bool pending = false;
+    for (uint32_t pc : set) pending = pending || is_assertion(_p._prog[pc]);
+    if (!pending) flags = 0;  // nothing in the state looks at its neighbours
     std::string key(reinterpret_cast<const char*>(set.data()), set.size() * sizeof(uint32_t));
     key.push_back(acc ? 1 : 0);
+    key.push_back(static_cast<char>(flags));
     auto it = _index.find(key);
     if (it != _index.end()) return it->second;
     const int32_t id = static_cast<int32_t>(_sets.size());
     _sets.push_back(std::move(set));
     _accept.push_back(acc ? 1 : 0);
+    _flags.push_back(flags);
+    _eot.push_back(-1);
     _next.resize(_next.size() + 256, -1);
     _index.emplace(std::move(key), id);
     return id;
@@ -752,10 +852,13 @@ class Dfa {
   }
 
   const Program& _p;
-  const bool _usable;
+  const bool _assert;  // the program holds assertions: states carry flags, transitions resolve them (expand)
   int32_t _start = 0;
   std::vector<std::vector<uint32_t>> _sets;  // state -> its program counters (sorted)
   std::vector<uint8_t> _accept;
+  std::vector<uint8_t> _flags;               // assertion programs: FLAG_* of the position the state stands at
+  std::vector<int8_t> _eot;                  // assertion programs: does the state match at the end of the line (-1 = unknown)
+  std::vector<uint32_t> _cons;               // scratch of expand()
   std::vector<int32_t> _next;                // state x byte -> state, -1 = not built yet
   std::unordered_map<std::string, int32_t> _index;
   std::vector<uint32_t> _mark, _stack;

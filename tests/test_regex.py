@@ -326,3 +326,48 @@ def test_vm_matches_re2_on_random_expressions(host_check, tmp_path):
         assert got == exp, (expr, icase)
         checked += 1
     assert checked > 60, checked
+
+
+def test_dfa_resolves_assertions(host_check, tmp_path):
+    """Programs with ^ $ \\b \\B run on the lazy DFA too (pending assertions + position flags in the states,
+    regex_vm::Dfa::expand).  Assertion-heavy random expressions over short words: regex_host_check exits 3 when the
+    DFA and the Pike VM disagree on any line, and its line count must equal Python's re (ASCII \\b on bytes) as well."""
+    import re
+    rng = np.random.default_rng(int(os.environ.get("XS_REGEX_SEED", "5")))
+    alphabet = list("ab_1 -")
+    lines = ["".join(rng.choice(alphabet, p=[0.3, 0.25, 0.05, 0.1, 0.25, 0.05]) for _ in range(int(rng.integers(0, 14))))
+             for _ in range(800)]
+    path = tmp_path / "words.txt"
+    path.write_text("\n".join(lines) + "\n")
+    raw = [ln.encode() for ln in lines]
+
+    def piece():
+        r = rng.random()
+        if r < 0.35:
+            return rng.choice(["\\b", "\\B", "^", "$"])
+        if r < 0.75:
+            return "".join(rng.choice(list("ab1")) for _ in range(int(rng.integers(1, 3))))
+        if r < 0.85:
+            return rng.choice(["[ab]", "[^a ]", "\\w", "\\W", ".", " "])
+        if r < 0.93:
+            return rng.choice(["a*", "b+", "[ab]?", "\\w{1,2}", " *"])
+        return "(" + "|".join("".join(piece2() for _ in range(int(rng.integers(1, 4)))) for _ in range(2)) + ")"
+
+    def piece2():
+        return rng.choice(["\\b", "\\B", "$", "^", "a", "b", "ab", "1", "\\w", " "])
+
+    checked = with_assertion = 0
+    for _ in range(260):
+        expr = "".join(piece() for _ in range(int(rng.integers(2, 6))))
+        out = subprocess.run([host_check, "count_lines", expr, str(path)], capture_output=True, text=True)
+        if out.returncode == 1:  # no required literal
+            continue
+        assert out.returncode == 0, (expr, out.stderr)
+        try:
+            cre = re.compile(expr.encode())
+        except re.error:
+            continue
+        assert int(out.stdout) == sum(1 for r in raw if cre.search(r)), expr
+        checked += 1
+        with_assertion += any(t in expr for t in ("\\b", "\\B", "^", "$"))
+    assert checked > 80 and with_assertion > 50, (checked, with_assertion)
