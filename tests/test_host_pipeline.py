@@ -16,7 +16,6 @@ difference between the double and the CUDA path, not a host-pipeline bug.
 Also here: the same driver under ThreadSanitizer (readers + pusher + verification threads + a live consumer), and the
 failure path (an injected push failure closes the result, reports the error, leaves no thread behind)."""
 import os
-import shutil
 import subprocess
 
 import numpy as np
@@ -52,19 +51,46 @@ def _build(name, flags, main_src=None):
     return exe
 
 
-@pytest.fixture(scope="module")
-def double():
-    return _build("xsgrep_double", ["-O2"])
+VARIANTS = {
+    "xsgrep_double": (["-O2"], None),
+    "xsgrep_double_tsan": (["-O1", "-g", "-fsanitize=thread"], None),
+    "xsgrep_double_asan": (["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"], None),
+    "reference_usage": (["-O2"], os.path.join(CPP, "reference_usage.cpp")),
+}
 
 
 @pytest.fixture(scope="module")
-def double_tsan():
-    if shutil.which("g++") is None:
-        pytest.skip("no compiler")
-    try:
-        exe = _build("xsgrep_double_tsan", ["-O1", "-g", "-fsanitize=thread"])
-    except subprocess.CalledProcessError:
-        pytest.skip("ThreadSanitizer runtime not available")
+def built():
+    """All variants compiled side by side (each is ~25 s of g++ on the header-only host layer)."""
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(len(VARIANTS)) as pool:
+        jobs = {name: pool.submit(_build, name, *spec) for name, spec in VARIANTS.items()}
+        out = {}
+        for name, job in jobs.items():
+            try:
+                out[name] = job.result()
+            except subprocess.CalledProcessError as e:
+                out[name] = e
+    return out
+
+
+def _variant(built, name, what):
+    exe = built[name]
+    if isinstance(exe, Exception):
+        if name == "xsgrep_double" or name == "reference_usage":
+            raise exe
+        pytest.skip(what + " runtime not available")
+    return exe
+
+
+@pytest.fixture(scope="module")
+def double(built):
+    return _variant(built, "xsgrep_double", "")
+
+
+@pytest.fixture(scope="module")
+def double_tsan(built):
+    exe = _variant(built, "xsgrep_double_tsan", "ThreadSanitizer")
     probe = subprocess.run([exe, "--selftest-host"], capture_output=True, text=True)
     if probe.returncode != 0 and "ThreadSanitizer" not in probe.stderr:
         pytest.skip("ThreadSanitizer binaries do not run here: " + probe.stderr[-200:])
@@ -72,11 +98,8 @@ def double_tsan():
 
 
 @pytest.fixture(scope="module")
-def double_asan():
-    try:
-        exe = _build("xsgrep_double_asan", ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"])
-    except subprocess.CalledProcessError:
-        pytest.skip("AddressSanitizer runtime not available")
+def double_asan(built):
+    exe = _variant(built, "xsgrep_double_asan", "AddressSanitizer")
     probe = subprocess.run([exe, "--selftest-host"], capture_output=True, text=True)
     if probe.returncode != 0 and "Sanitizer" not in probe.stderr:
         pytest.skip("sanitizer binaries do not run here: " + probe.stderr[-200:])
@@ -120,11 +143,11 @@ def test_regex(double, tmp_path):
     rx.check_extern_search_regex(golden, rx.corpora(), double, tmp_path)
 
 
-def test_reference_call_shapes(tmp_path):
+def test_reference_call_shapes(built, tmp_path):
     """tests/cpp/reference_usage.cpp: every call shape the reference's README, examples and tests use (overloads, a
     char* meta path, join + size, copyResultSafe, live loops, running totals, an ignored searcher) compiles against
     xsearch.hpp and returns what the oracle says."""
-    exe = _build("reference_usage", ["-O2"], os.path.join(CPP, "reference_usage.cpp"))
+    exe = _variant(built, "reference_usage", "")
     oracle, _ = oracle_lib.load(build=False)
     rng = np.random.default_rng(12)
     words = [b"Needle", b"needle", b"NEEDLE", b"nneedle", b"hay", b"stack of", b""]
