@@ -8,13 +8,13 @@
 // (SURVEY.md 0.1/0.3): v1 chunking is done by the caller (bounds array), chunks are copied
 // into xs::strtype like the reference's FileReader does (tasks/readers.h:39-48), per-chunk
 // results are globalised (+chunk base) and concatenated in file order, and line indices
-// are derived from byte_offsets_line by counting '\n' with the reference's own
-// simd::findNextNewLine.
+// are derived from byte_offsets_line by counting '\n' in one pass per chunk (std::count).
 #include <xsearch/string_search/search_wrappers.h>
 #include <xsearch/string_search/simd_search.h>
 #include <xsearch/types.h>
 #include <xsearch/utils/string_utils.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <cstring>
@@ -33,16 +33,12 @@ struct Part {
   uint64_t count = 0, newlines = 0;
 };
 
+// '\n' in d[from, to): ONE vectorised pass (std::count).  v1 answered xs::line_indices from the meta file's
+// line-index mapping plus a short newline count (metafile_cat.cpp:47-49); that mapping is absent from the snapshot, so
+// the harness counts.  Round 1 counted with one simd::findNextNewLine call per newline, which cost the timed
+// baseline more than the search itself.
 uint64_t count_newlines(const xs::strtype& d, uint64_t from, uint64_t to) {
-  uint64_t c = 0;
-  size_t shift = from;
-  while (shift < to) {
-    int64_t e = xs::search::simd::findNextNewLine(d.data(), to, shift);
-    if (e < 0) break;
-    c++;
-    shift = static_cast<size_t>(e) + 1;
-  }
-  return c;
+  return static_cast<uint64_t>(std::count(d.data() + from, d.data() + to, '\n'));
 }
 
 void search_chunk(const char* p, uint64_t n, const std::string& pat, int kind, int skip_to_nl, Part* out) {

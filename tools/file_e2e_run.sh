@@ -12,8 +12,8 @@ sys.path.insert(0, os.getcwd())
 import bench, xsearch_b200 as xs
 gib, path = int(sys.argv[1]), sys.argv[2]
 # the default workload's corpus (needle, rate and seed of bench.py), generated on the host cores
-tags, pat, needle, rate, seed, nbytes = bench.WORKLOADS[bench.DEFAULT_WORKLOAD]
-bench.host_sample(xs, gib << 30, needle, rate, seed, os.cpu_count() or 8).tofile(path)
+tags, pat, needle, rate, seed, nbytes, scaling = bench.WORKLOADS[bench.DEFAULT_WORKLOAD]
+bench.host_corpus(gib << 30, needle, rate, seed, os.cpu_count() or 8).tofile(path)
 EOF
 ls -l $F > $O
 echo "host cores: $(nproc)" >> $O

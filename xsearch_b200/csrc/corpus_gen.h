@@ -25,27 +25,44 @@ struct xs_vocab_t {
 
 #define XS_VOCAB_INIT {XS_VOCAB_CHARS, {XS_VOCAB_LENS}}
 
-XS_HD uint64_t xs_splitmix64(uint64_t& s) {
-  s += 0x9E3779B97F4A7C15ull;
-  uint64_t z = s;
+// the splitmix64 finaliser (a bijection of 64-bit words)
+XS_HD uint64_t xs_mix64(uint64_t z) {
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
   return z ^ (z >> 31);
 }
 
+// One independent stream per block: start AND increment are hashes of (seed, block), so no two blocks walk the
+// same sequence.  (Round 1 seeded block b with seed * C + b * phi and stepped by the same phi: draw j of block b
+// was draw j - 1 of block b + 1, every block its neighbour shifted by one word.)
+struct xs_rng {
+  uint64_t s, inc;
+};
+XS_HD xs_rng xs_rng_for_block(uint64_t seed, uint64_t blk) {
+  xs_rng g;
+  const uint64_t h = xs_mix64(seed * 0xD1342543DE82EF95ull + 0x1234567ull) ^ xs_mix64(blk + 0x9E3779B97F4A7C15ull);
+  g.s = xs_mix64(h);
+  g.inc = xs_mix64(h ^ 0xDA942042E4DD58B5ull) | 1ull;
+  return g;
+}
+XS_HD uint64_t xs_next(xs_rng& g) {
+  g.s += g.inc;
+  return xs_mix64(g.s);
+}
+
 // Writes exactly XSG_SYNTH_BLOCK bytes of block `blk` to out (any byte-addressable memory).
 XS_HD void xs_synth_block(uint8_t* out, uint64_t blk, const xsg_synth_params& p, const xs_vocab_t& voc) {
-  uint64_t s = p.seed * 0xD1342543DE82EF95ull + blk * 0x9E3779B97F4A7C15ull + 0x1234567ull;
+  xs_rng s = xs_rng_for_block(p.seed, blk);
   uint32_t pos = 0;
   uint32_t words_in_line = 0, line_target = 1, inject_word = 0xffffffffu;
   const uint32_t reserve = 16 + (p.needle_len > 12 ? p.needle_len : 12);
   while (XSG_SYNTH_BLOCK - pos >= reserve) {
-    uint64_t r = xs_splitmix64(s);
+    uint64_t r = xs_next(s);
     if (words_in_line == 0) {
       line_target = 1 + (uint32_t)(r & 0xffff) % 12;
       bool inject = p.needle_len > 0 && (uint32_t)(r >> 32) < p.needle_rate_u32;
       inject_word = inject ? (uint32_t)((r >> 16) & 0xffff) % line_target : 0xffffffffu;
-      r = xs_splitmix64(s);
+      r = xs_next(s);
     }
     if (words_in_line == inject_word) {
       for (uint32_t k = 0; k < p.needle_len; ++k) out[pos++] = p.needle[k];
