@@ -476,8 +476,7 @@ def run_ours(args):
                 # shard summaries travel as peer stores over NVLink (xsg_exchange, repo:xsearch_b200/csrc/xsg_exchange.cu)
                 ex = xs.Exchange(ctx)
                 for _ in range(2):
-                    res = ctx.scan(corpus, pat, kinds, offset_base=shard_base)
-                    ex.push()
+                    res = ctx.scan(corpus, pat, kinds, offset_base=shard_base, publish=True)
                     ex.rebase(res)
                     res.free()
             elif world > 1:  # first use of the collective the timed loop relies on
@@ -487,10 +486,9 @@ def run_ours(args):
 
             def resident_step():
                 if ex is not None:
-                    # scan + push of the shard summary into every rank's table + fix-up kernel that waits for the
-                    # round on the device: no host round trip, no collective call
-                    r = ctx.scan(corpus, pat, kinds, offset_base=shard_base)
-                    ex.push()
+                    # the scan's last kernel stores the shard summary into every rank's table; the fix-up kernel waits
+                    # for the round on the device: no host round trip, no collective call, one launch
+                    r = ctx.scan(corpus, pat, kinds, offset_base=shard_base, publish=True)
                     ex.rebase(r)
                 elif world > 1:
                     # scan + all-gather of the device-resident shard summaries + on-device line-index fix-up
@@ -517,7 +515,7 @@ def run_ours(args):
                 if world == 1:
                     results = res.count(xs.TAGS[tags[-1]])
                 t = res.timings()
-                launches += t.kernel_launches + (2 if ex is not None else (1 if world > 1 and rank > 0 and want_idx else 0))
+                launches += t.kernel_launches + (1 if ex is not None else (1 if world > 1 and rank > 0 and want_idx else 0))
                 main_ms.append(t.main_kernel_ms)
                 raw = res.raw_occurrences
                 res.free()

@@ -34,6 +34,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdint>
 #include <cstdlib>
@@ -90,6 +91,11 @@ struct lines {
 // knobs the reference does not have (device selection, chunking); defaults reproduce v1 chunking
 struct Options {
   int device = 0;
+  // more than one entry: ONE Searcher over several devices of this host (the reference's num_threads workers over the
+  // chunks of one file, Searcher.h:141-145): segments are dealt round-robin to the devices, results are published in
+  // file order, line indices get their base on the host (the '\n' count of the earlier segments).  Literal patterns
+  // only; a regular expression runs on devices[0].  Empty: {device}.
+  std::vector<int> devices;
   uint64_t min_chunk = XSG_DEFAULT_MIN_CHUNK;   // v1: chunks of >= 16 MiB, extended through the next '\n'
   uint64_t segment_bytes = 256ull << 20;        // bytes read / copied / scanned per pipeline step
   bool ignore_case = false;                     // set by the ignore_case overloads of extern_search
@@ -340,22 +346,37 @@ class Searcher {
       plan(meta_file_path);
       xsg_scan_opts so{};
       so.flags = _opt.ignore_case ? XSG_SCAN_IGNORE_CASE : 0u;  // ASCII fold, like v1's tolower processor
-      // literal: one stream of the asked kind.  regex: one stream per required literal (each with a context of its
-      // own: the staging buffers belong to the context), reporting candidate lines with their indices
+      // literal: one lane per device, each with one stream of the asked kind.  regex: one lane (devices[0]) with one
+      // stream per required literal (each with a context of its own: the staging buffers belong to the context),
+      // reporting candidate lines with their indices
+      std::vector<int> devs = _opt.devices.empty() ? std::vector<int>{_opt.device} : _opt.devices;
+      if (_regex_mode) devs.resize(1);
       const uint32_t kinds = _regex_mode ? (XSG_LINE_BYTE_OFFSETS | XSG_LINE_INDICES) : Tag::kind;
-      for (const std::string& lit : literals) {
-        xsg_ctx* ctx = nullptr;
-        if (xsg_init(_opt.device, &ctx) != XSG_OK) throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init"));
-        _ctxs.push_back(ctx);
-        xsg_stream* st = nullptr;
-        if (xsg_stream_open(ctx, reinterpret_cast<const uint8_t*>(lit.data()), static_cast<uint32_t>(lit.size()), kinds, &so,
-                            &st) != XSG_OK)
-          throw std::runtime_error(detail::last_error("xs::extern_search: xsg_stream_open"));
-        _streams.push_back(st);
+      if (devs.size() > 1) so.flags |= XSG_SCAN_LOCAL_LINE_INDEX;  // bases are added in harvest(), in file order
+      _lanes.resize(devs.size());
+      if (devs.size() > 1) {
+        std::vector<xsg_ctx*> cs(devs.size(), nullptr);
+        if (xsg_init_multi(devs.data(), static_cast<int>(devs.size()), cs.data()) != XSG_OK)
+          throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init_multi"));
+        for (size_t d = 0; d < devs.size(); ++d) _lanes[d].ctxs.push_back(cs[d]);
+      }
+      for (size_t d = 0; d < devs.size(); ++d) {
+        for (size_t k = 0; k < literals.size(); ++k) {
+          const std::string& lit = literals[k];
+          if (_lanes[d].ctxs.size() <= k) {
+            xsg_ctx* ctx = nullptr;
+            if (xsg_init(devs[d], &ctx) != XSG_OK) throw std::runtime_error(detail::last_error("xs::extern_search: xsg_init"));
+            _lanes[d].ctxs.push_back(ctx);
+          }
+          xsg_stream* st = nullptr;
+          if (xsg_stream_open(_lanes[d].ctxs[k], reinterpret_cast<const uint8_t*>(lit.data()), static_cast<uint32_t>(lit.size()),
+                              kinds, &so, &st) != XSG_OK)
+            throw std::runtime_error(detail::last_error("xs::extern_search: xsg_stream_open"));
+          _lanes[d].streams.push_back(st);
+        }
       }
     } catch (...) {
-      for (xsg_stream* st : _streams) xsg_stream_abort(st);
-      for (xsg_ctx* ctx : _ctxs) xsg_destroy(ctx);
+      destroy_lanes();
       if (_map) ::munmap(const_cast<uint8_t*>(_map), static_cast<size_t>(_size));
       ::close(_fd);
       throw;
@@ -366,10 +387,8 @@ class Searcher {
 
   ~Searcher() {
     join();
-    for (xsg_stream* st : _streams)
-      if (st) xsg_stream_abort(st);
     _bufs.clear();
-    for (xsg_ctx* ctx : _ctxs) xsg_destroy(ctx);
+    destroy_lanes();
     if (_map) ::munmap(const_cast<uint8_t*>(_map), static_cast<size_t>(_size));
     if (_fd >= 0) ::close(_fd);
   }
@@ -386,6 +405,9 @@ class Searcher {
     _running.store(false);
   }
   [[nodiscard]] bool running() const { return _running.load(); }
+  [[nodiscard]] size_t num_devices() const { return _lanes.size(); }
+  // host time spent page-locking the segment buffers (part of the pipeline time; valid after join())
+  [[nodiscard]] double pinned_alloc_ms() const { return _pinned_alloc_ms; }
   ResultT* getResult() { return &_result; }
   // nothing throws after extern_search returned: a failure closes the result early and is reported here
   [[nodiscard]] bool ok() const { return !_failed.load(); }
@@ -398,6 +420,23 @@ class Searcher {
   uint64_t bytes() const { return _size; }
 
  private:
+  // one device: its context(s) and stream(s) (literal: one of each; regex: one per required literal)
+  struct Lane {
+    std::vector<xsg_ctx*> ctxs;
+    std::vector<xsg_stream*> streams;
+    uint64_t parts_done = 0;  // parts of this lane's result that have been harvested
+  };
+
+  void destroy_lanes() {
+    for (Lane& l : _lanes) {
+      for (xsg_stream* st : l.streams)
+        if (st) xsg_stream_abort(st);
+      for (xsg_ctx* ctx : l.ctxs)
+        if (ctx) xsg_destroy(ctx);
+    }
+    _lanes.clear();
+  }
+
   // ---- planning: which byte ranges are read as one block --------------------------------------------
   void plan(const std::string& meta_file_path) {
     if (!meta_file_path.empty()) {
@@ -518,6 +557,7 @@ class Searcher {
     const uint8_t* ptr = nullptr;           // first byte of the segment on the host
     uint64_t goff = 0;                      // its global file offset
     uint64_t len = 0;                       // bytes of it that were pushed (whole chunks)
+    size_t lane = 0;                        // the device lane it was pushed to
   };
 
   // ---- results of one finished part -> the result collector ------------------------------------------
@@ -530,6 +570,14 @@ class Searcher {
     } else if constexpr (std::is_same_v<value_type, uint64_t>) {
       typename ResultT::part_type v(n);  // default-initialised: the copy below writes every element
       if (n && xsg_result_part_copy(res, part, Tag::kind, v.data(), n) != XSG_OK) return false;
+      if constexpr (Tag::kind == XSG_LINE_INDICES) {
+        // several devices: every part numbered its lines from its own first byte; parts are harvested in file
+        // order, so the base -- the '\n' count of everything before this segment -- is known here
+        if (_lanes.size() > 1) {
+          for (uint64_t& x : v) x += _newlines_seen;
+          _newlines_seen += xsg_result_part_newlines(res, part);
+        }
+      }
       _result.add(std::move(v));
     } else {
       std::vector<uint64_t> st(n), ln(n);
@@ -665,15 +713,17 @@ class Searcher {
     return true;
   }
 
-  // results of every part that has finished since the last call (literal: one stream; regex: all of them)
+  // results of every part of the segment's lane that has finished since the last call (literal: one stream; regex:
+  // all streams of the lane)
   template <class GetResult>
-  bool harvest_finished(GetResult&& result_of, uint64_t* parts_done, const Inflight& seg) {
+  bool harvest_finished(GetResult&& result_of, const Inflight& seg) {
+    Lane& lane = _lanes[seg.lane];
     std::vector<const xsg_result*> rs;
-    for (size_t k = 0; k < _streams.size(); ++k) rs.push_back(result_of(k));
-    while (*parts_done < xsg_result_num_parts(rs[0])) {
-      const bool ok = _regex_mode ? harvest_regex(rs, *parts_done, seg) : harvest(rs[0], *parts_done, seg);
+    for (size_t k = 0; k < lane.streams.size(); ++k) rs.push_back(result_of(k));
+    while (lane.parts_done < xsg_result_num_parts(rs[0])) {
+      const bool ok = _regex_mode ? harvest_regex(rs, lane.parts_done, seg) : harvest(rs[0], lane.parts_done, seg);
       if (!ok) return false;
-      ++*parts_done;
+      ++lane.parts_done;
     }
     return true;
   }
@@ -702,23 +752,27 @@ class Searcher {
   }
 
   void pusher_body() {
-    // one block being read (two around a block edge), one being copied to the device, one whose results are collected
-    const size_t nbuf = 4;
+    // per device lane one segment being copied / scanned and one whose results are collected, plus the block(s) being
+    // read (two around a block edge)
+    const size_t nlanes = _lanes.size();
+    const size_t nbuf = nlanes + 3;
+    const auto t_alloc = std::chrono::steady_clock::now();
     for (size_t i = 0; i < nbuf && i < _blocks.size() + 1 && !_blocks.empty(); ++i) {
       auto b = std::make_unique<detail::Pinned>();
       if (!b->alloc(static_cast<size_t>(_headroom + _max_block + 64))) throw std::runtime_error(detail::last_error("pinned buffer"));
       _bufs.push_back(std::move(b));
       _free.push_back(static_cast<int>(i));
     }
+    _pinned_alloc_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_alloc).count();
     _ready.assign(_blocks.size(), -1);
     _slices_left.assign(_blocks.size(), 0);
     for (int t = 0; t < _num_readers; ++t) _readers.emplace_back(&Searcher::run_reader, this);
 
-    Inflight prev;          // pushed, results not collected yet
-    Inflight carry_holder;  // holds the bytes of `carry` when they belong to a segment that was not pushed
+    std::deque<Inflight> pending;  // pushed, results not collected yet: file order, at most one per lane + the newest
+    Inflight carry_holder;         // holds the bytes of `carry` when they belong to a segment that was not pushed
     const uint8_t* carry = nullptr;
     uint64_t carry_len = 0;
-    uint64_t parts_done = 0;
+    uint64_t n_pushed = 0;
     std::vector<uint64_t> bounds;
 
     for (size_t i = 0; i < _blocks.size(); ++i) {
@@ -780,34 +834,55 @@ class Searcher {
         continue;
       }
       if (_regex_mode) bounds.assign(1, consumed);  // re2 has no chunk-tail behaviour to reproduce (see harvest_regex)
-      for (xsg_stream* st : _streams)
-        if (xsg_stream_push(st, cur.ptr, consumed, bounds.data(), bounds.size(), nullptr) != XSG_OK)
+      cur.lane = static_cast<size_t>(n_pushed++ % nlanes);
+      Lane& lane = _lanes[cur.lane];
+      for (xsg_stream* st : lane.streams)
+        if (xsg_stream_push_at(st, cur.ptr, consumed, bounds.data(), bounds.size(), cur.goff, nullptr) != XSG_OK)
           throw std::runtime_error(detail::last_error("xsg_stream_push"));
-      // the previous segment was scanned inside this push: publish its results, free its buffer
-      if (!harvest_finished([&](size_t k) { return xsg_stream_result(_streams[k]); }, &parts_done, prev))
-        throw std::runtime_error(detail::last_error("result copy"));
-      if (prev.valid) release(prev);
-      prev = std::move(cur);
+      // this lane's previous segment was scanned inside the push: it is the oldest one pending (segments go to the
+      // lanes in turn) -- publish its results, free its buffer
+      pending.push_back(std::move(cur));
+      if (pending.size() > nlanes) {
+        Inflight& done = pending.front();
+        if (!harvest_finished([&](size_t k) { return xsg_stream_result(_lanes[done.lane].streams[k]); }, done))
+          throw std::runtime_error(detail::last_error("result copy"));
+        release(done);
+        pending.pop_front();
+      }
     }
-    std::vector<xsg_result*> fin(_streams.size(), nullptr);
-    bool closed = true;
-    for (size_t k = 0; k < _streams.size(); ++k) {
-      xsg_stream* st = _streams[k];
-      _streams[k] = nullptr;  // close destroys it whatever happens
-      closed = xsg_stream_close(st, &fin[k]) == XSG_OK && closed;
+    // the last segment of every lane is scanned when its streams are closed: in file order
+    std::string close_error;
+    bool ok = true;
+    while (!pending.empty()) {
+      Inflight& seg = pending.front();
+      Lane& lane = _lanes[seg.lane];
+      std::vector<xsg_result*> fin(lane.streams.size(), nullptr);
+      bool closed = true;
+      for (size_t k = 0; k < lane.streams.size(); ++k) {
+        xsg_stream* st = lane.streams[k];
+        lane.streams[k] = nullptr;  // close destroys it whatever happens
+        if (st) closed = xsg_stream_close(st, &fin[k]) == XSG_OK && closed;
+        else closed = false;
+      }
+      if (!closed && close_error.empty()) close_error = detail::last_error("xsg_stream_close");
+      if (closed && ok && close_error.empty())
+        ok = harvest_finished([&](size_t k) { return static_cast<const xsg_result*>(fin[k]); }, seg);
+      if (fin[0]) {
+        xsg_timings t{};
+        xsg_result_timings(fin[0], &t);
+        _timings.scan_ms += t.scan_ms;
+        _timings.main_kernel_ms += t.main_kernel_ms;
+        _timings.post_ms += t.post_ms;
+        _timings.kernel_launches += t.kernel_launches;
+        _timings.h2d_ms = std::max(_timings.h2d_ms, t.h2d_ms);
+      }
+      for (xsg_result* r : fin)
+        if (r) xsg_result_free(r);
+      release(seg);
+      pending.pop_front();
     }
-    const std::string close_error = closed ? std::string() : detail::last_error("xsg_stream_close");
-    bool ok = closed && harvest_finished([&](size_t k) { return static_cast<const xsg_result*>(fin[k]); }, &parts_done, prev);
-    if (fin[0]) xsg_result_timings(fin[0], &_timings);
-    for (xsg_result* r : fin)
-      if (r) xsg_result_free(r);
-    if (!closed) {
-      if (prev.valid) release(prev);
-      if (carry_holder.valid) release(carry_holder);
-      throw std::runtime_error(close_error);
-    }
-    if (prev.valid) release(prev);
     if (carry_holder.valid) release(carry_holder);
+    if (!close_error.empty()) throw std::runtime_error(close_error);
     if (!ok) throw std::runtime_error(detail::last_error("result copy"));
     if constexpr (Tag::is_count) {
       if (!_published) _result.add(typename ResultT::part_type{0});  // empty input: the only running total is 0
@@ -824,13 +899,13 @@ class Searcher {
   std::vector<detail::Block> _blocks;
   uint64_t _max_block = 0, _headroom = 0;
 
-  std::vector<xsg_ctx*> _ctxs;        // literal: one; regex: one per required literal
-  std::vector<xsg_stream*> _streams;  // the stream of each context
+  std::vector<Lane> _lanes;           // one per device (regex: one lane)
   xsg_timings _timings{};
+  double _pinned_alloc_ms = 0;
   bool _regex_mode = false;
   std::unique_ptr<LineVerifier> _verifier;
   std::vector<std::unique_ptr<LineVerifier::Cache>> _caches;  // regex mode: per verification thread, kept across parts
-  uint64_t _newlines_seen = 0;  // regex mode: '\n' in all harvested segments
+  uint64_t _newlines_seen = 0;  // regex mode / several devices: '\n' in all harvested segments
 
   mutable std::mutex _m;  // guards _free, _ready, _next_block, _next_slice, _cur_buf, _slices_left, _error
   std::condition_variable _cv;

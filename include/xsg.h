@@ -76,6 +76,14 @@ typedef struct xsg_scan_opts {
  * (simd::toLower, src/utils/string_utils.cpp:11-33: ASCII A-Z only) and searched the lowered pattern in
  * the lowered bytes.  Here the fold happens in registers while the bytes are scanned. */
 #define XSG_SCAN_IGNORE_CASE 1u
+/* xsg_scan only: the scan's last kernel stores the scan's summary into every rank's table of the exchange attached
+ * to the context (xsg_exchange_create) -- the publish step of the multi-GPU exchange without a launch of its own;
+ * replaces the xsg_exchange_push() call of that round */
+#define XSG_SCAN_PUBLISH 2u
+/* streams only: the line indices of every part count from the part's own first byte (+ line_index_base) instead of
+ * from the first byte of the stream -- for callers that deal the segments of one file to several streams/devices
+ * and add each part's base themselves (the '\n' count of the earlier parts, xsg_result_part_newlines) */
+#define XSG_SCAN_LOCAL_LINE_INDEX 4u
 
 typedef struct xsg_timings {
   float scan_ms;        /* all device work of the scan (CUDA events on the library's stream) */
@@ -100,6 +108,9 @@ int xsg_version(void);
 
 /* ---- context -------------------------------------------------------------------------- */
 int xsg_init(int device, xsg_ctx** out);
+/* one host process, n devices: out[0..n) = one context per device, peer access enabled between them where the
+ * hardware allows (NVLink / NVSwitch); nothing is left behind on failure.  Each context is destroyed on its own. */
+int xsg_init_multi(const int* devices, int n, xsg_ctx** out);
 void xsg_destroy(xsg_ctx* ctx);
 int xsg_device_info(xsg_ctx* ctx, int* sm_count, uint64_t* total_mem, char* name, size_t name_cap);
 /* run all device work of this context on a caller-owned CUDA stream (a cudaStream_t passed as
@@ -141,6 +152,14 @@ int xsg_scan(xsg_ctx* ctx, const xsg_corpus* c, const uint8_t* pattern, uint32_t
 int xsg_search_host(xsg_ctx* ctx, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb,
                     uint64_t min_chunk, const uint8_t* pattern, uint32_t m, uint32_t kinds,
                     const xsg_scan_opts* opts, xsg_result** out);
+/* the same search on n_ctx devices driven by ONE host thread (the reference's num_threads workers over the chunks
+ * of one file, include/xsearch/Searcher.h:141-145, README.md:72): the segments are dealt round-robin to the devices,
+ * every device copies and scans its own, and ONE result comes back with its parts in file order, byte offsets and
+ * line indices global (a part's line-index base is the '\n' count of the parts before it, known on the host one
+ * segment later: no collective).  The result belongs to ctxs[0]; all contexts must outlive it. */
+int xsg_search_host_multi(xsg_ctx* const* ctxs, int n_ctx, const void* host, uint64_t n, const uint64_t* bounds,
+                          uint64_t nb, uint64_t min_chunk, const uint8_t* pattern, uint32_t m, uint32_t kinds,
+                          const xsg_scan_opts* opts, xsg_result** out);
 
 /* ---- streamed search (the reference's reader -> searcher -> result loop, Searcher.h:100-120,
  *      tasks/readers.h:39-48, as a push interface) -------------------------------------------------
@@ -156,6 +175,10 @@ int xsg_stream_open(xsg_ctx* ctx, const uint8_t* pattern, uint32_t m, uint32_t k
                     xsg_stream** out);
 int xsg_stream_push(xsg_stream* st, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb,
                     uint64_t* ticket);
+/* the same with the segment's offset in the stream given by the caller (xsg_stream_push continues behind the previous
+ * segment): segments of one file dealt to several streams keep their global byte offsets */
+int xsg_stream_push_at(xsg_stream* st, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb,
+                       uint64_t stream_offset, uint64_t* ticket);
 int xsg_stream_wait_copied(xsg_stream* st, uint64_t ticket);
 const xsg_result* xsg_stream_result(const xsg_stream* st);
 int xsg_stream_close(xsg_stream* st, xsg_result** out);
@@ -193,23 +216,32 @@ int xsg_result_rebase_from_table(xsg_result* r, const uint64_t* table_dev, uint3
 void xsg_result_free(xsg_result* r);
 
 /* ---- shard exchange over NVLink peer memory (no counterpart in the single-host reference) ------
- * One process per GPU.  Every rank creates an exchange, hands its 64-byte handle to all other ranks (any
- * transport: a process group, MPI, a file) and connects with the handles of all ranks in rank order.  After each
- * scan, xsg_exchange_push() launches a kernel that writes the scan's summary {newlines, matches, matching lines,
- * lines} into the table of EVERY rank -- plain stores over NVLink into memory opened with cudaIpcOpenMemHandle,
- * then a system-scope release of the round number.  xsg_result_rebase_exchanged() launches the fix-up kernel: it
- * waits (on the device) until all ranks have published this round and adds the newline counts of the lower ranks
- * to the result's line indices.  No host round trip and no collective-library call is involved; both calls must
- * be made by every rank once per round, in this order.  xsg_exchange_totals() waits for the round and copies the
- * gathered table [world][4] to the host.  The same fix-up through an NCCL all-gather: xsg_scan_summary_device +
- * xsg_result_rebase_from_table. */
+ * A rank is one context: a process with one GPU (handles travel between the processes by any transport -- a process
+ * group, MPI, a file -- and xsg_exchange_connect maps the peers' tables with cudaIpcOpenMemHandle), or one of several
+ * contexts of one process (xsg_init_multi + xsg_exchange_connect_local: peer access, no handles).  A context has at
+ * most one exchange.  Per round, every rank
+ *   1. publishes the summary {newlines, matches, matching lines, lines} of its shard into the table of EVERY rank --
+ *      plain stores over NVLink, then a system-scope release of the round number -- either from inside the scan
+ *      (xsg_scan with XSG_SCAN_PUBLISH: the scan's last kernel does it, no extra launch) or with xsg_exchange_push()
+ *      for a finished result (any number of parts, e.g. a streamed one: its totals are known on the host);
+ *   2. waits for the round: xsg_result_rebase_exchanged() launches the fix-up kernel, which spins on the device until
+ *      all ranks have published this round and adds the newline counts of the lower ranks to the result's line
+ *      indices; xsg_exchange_totals() waits and copies the gathered table [world][4] to the host.
+ * No host round trip and no collective-library call is involved.  Publishing a round before the previous one was
+ * waited for is XSG_ERR_STATE (the two slot parities would be overrun).  A wait that times out (60 s: a peer died)
+ * adds nothing and raises a flag that xsg_exchange_totals, xsg_exchange_check and every xsg_result_copy* of a
+ * rebased result report as XSG_ERR_STATE (and clear).  The same fix-up through an NCCL all-gather:
+ * xsg_scan_summary_device + xsg_result_rebase_from_table. */
 typedef struct xsg_exchange xsg_exchange;
 #define XSG_EXCHANGE_HANDLE_BYTES 64
+/* handle_out may be NULL when the exchange is only connected locally */
 int xsg_exchange_create(xsg_ctx* ctx, uint32_t world, uint32_t rank, xsg_exchange** out, void* handle_out);
 int xsg_exchange_connect(xsg_exchange* x, const void* handles /* world x XSG_EXCHANGE_HANDLE_BYTES */);
-int xsg_exchange_push(xsg_exchange* x);
+int xsg_exchange_connect_local(xsg_exchange* const* all /* [n], all[r] = rank r */, uint32_t n);
+int xsg_exchange_push(xsg_exchange* x, const xsg_result* r);
 int xsg_result_rebase_exchanged(xsg_result* r, xsg_exchange* x);
 int xsg_exchange_totals(xsg_exchange* x, uint64_t* table_host /* world x 4 */);
+int xsg_exchange_check(xsg_exchange* x); /* synchronizes the context's stream; XSG_ERR_STATE after a timed-out wait */
 void xsg_exchange_destroy(xsg_exchange* x);
 
 #ifdef __cplusplus

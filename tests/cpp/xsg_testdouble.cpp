@@ -72,6 +72,7 @@ struct xsg_stream {
   uint32_t kinds = 0;
   bool icase = false;
   uint64_t goff_base = 0, lidx = 0, bytes_pushed = 0, pushed = 0;
+  bool local_lidx = false;  // XSG_SCAN_LOCAL_LINE_INDEX
   bool last_terminated = true;
   long fail_push = -1;
   bool noscan = false;
@@ -132,7 +133,7 @@ int scan_pending(xsg_stream* st) {
     if (total) xso_lines(buf, n, pat, m, b, nb, p.line_starts.data(), p.line_lengths.data(), total, 1);
     for (uint64_t& x : p.line_starts) x += goff;
   }
-  st->lidx += p.newlines;
+  if (!st->local_lidx) st->lidx += p.newlines;
   st->pending = false;
   return XSG_OK;
 }
@@ -165,6 +166,12 @@ int xsg_init(int device, xsg_ctx** out) {
   *out = new (std::nothrow) xsg_ctx();
   if (!*out) return XSG_ERR_NOMEM;
   (*out)->device = device;
+  return XSG_OK;
+}
+int xsg_init_multi(const int* devices, int n, xsg_ctx** out) {  // any number of pretend devices
+  if (!devices || !out || n <= 0) return XSG_ERR_ARG;
+  for (int i = 0; i < n; ++i)
+    if (xsg_init(devices[i], &out[i]) != XSG_OK) return XSG_ERR_NOMEM;
   return XSG_OK;
 }
 void xsg_destroy(xsg_ctx* ctx) { delete ctx; }
@@ -211,6 +218,7 @@ int xsg_stream_open(xsg_ctx* ctx, const uint8_t* pattern, uint32_t m, uint32_t k
   st->kinds = kinds;
   st->goff_base = opts ? opts->global_offset_base : 0;
   st->lidx = opts ? opts->line_index_base : 0;
+  st->local_lidx = opts && (opts->flags & XSG_SCAN_LOCAL_LINE_INDEX);
   if (const char* f = std::getenv("XSG_DOUBLE_FAIL_PUSH")) st->fail_push = std::atol(f);
   st->noscan = std::getenv("XSG_DOUBLE_NOSCAN") != nullptr;
   st->res = new xsg_result();
@@ -220,6 +228,11 @@ int xsg_stream_open(xsg_ctx* ctx, const uint8_t* pattern, uint32_t m, uint32_t k
 }
 
 int xsg_stream_push(xsg_stream* st, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb, uint64_t* ticket) {
+  return xsg_stream_push_at(st, host, n, bounds, nb, st ? st->bytes_pushed : 0, ticket);
+}
+
+int xsg_stream_push_at(xsg_stream* st, const void* host, uint64_t n, const uint64_t* bounds, uint64_t nb,
+                       uint64_t stream_offset, uint64_t* ticket) {
   if (!st || !host || n == 0 || !bounds || nb == 0) {
     set_error("xsg_stream_push: a segment needs bytes and at least one chunk bound");
     return XSG_ERR_ARG;
@@ -248,14 +261,14 @@ int xsg_stream_push(xsg_stream* st, const void* host, uint64_t n, const uint64_t
   }
   st->pend_ptr = hbuf;
   st->pend_n = n;
-  st->pend_off = st->bytes_pushed;
+  st->pend_off = stream_offset;
   st->pend_sum = st->noscan ? 0 : checksum(hbuf, n);
   st->pend_bounds.assign(bounds, bounds + nb);
   st->pending = true;
   st->last_terminated = hbuf[n - 1] == '\n';
   if (ticket) *ticket = st->pushed;
   st->pushed += 1;
-  st->bytes_pushed += n;
+  st->bytes_pushed = stream_offset + n;
   return XSG_OK;
 }
 

@@ -191,6 +191,40 @@ def check_ignore_case(xsgrep, tmp_path):
     assert run_xsgrep(xsgrep, "count", b"SherLOCK", path, base[:-1]) == "0\n"
 
 
+def check_multi_device(xsgrep, tmp_path, devices):
+    """ONE Searcher over several devices (xs::Options::devices, xsgrep --devices): segments dealt round-robin, output
+    byte-identical to the oracle (= to the single-device run) for all six tags, also live, with a meta file's chunk
+    table, and when there are fewer segments than devices."""
+    import xsearch_b200 as xs
+    oracle, _ = oracle_lib.load(build=False)
+    p = xs.SynthParams.make(12, b"Sherlock", 30.0 / 8192)
+    buf = xs.synth_host(4096 * 5000, p)  # ~20 MB -> ~10 segments of 2 MiB
+    path = tmp_path / "multi.txt"
+    buf.tofile(path)
+    min_chunk, seg = 1 << 19, 2 << 20
+    bounds = oracle.chunk_bounds(buf, min_chunk)
+    dev = ["--devices", ",".join(str(d) for d in devices)]
+    base = ["--min-chunk", str(min_chunk), "--segment-bytes", str(seg)]
+    for pat in (b"Sherlock", b"the"):
+        for tag in TAGS:
+            exp = expected_output(oracle, buf, pat, bounds, tag)
+            assert run_xsgrep(xsgrep, tag, pat, path, base + dev) == exp, (tag, pat)
+            assert run_xsgrep(xsgrep, tag, pat, path, base + dev + ["--live", "--readers", "3", "-j", "2"]) == exp, (tag, pat, "live")
+    # one segment only: the other devices stay idle
+    big = ["--min-chunk", str(min_chunk), "--segment-bytes", str(1 << 30)]
+    for tag in ("line_indices", "lines", "count"):
+        assert run_xsgrep(xsgrep, tag, b"Sherlock", path, big + dev) == expected_output(oracle, buf, b"Sherlock", bounds, tag)
+    # chunk table from a meta file
+    meta = tmp_path / "multi.meta"
+    mb = oracle.chunk_bounds(buf, 300000)
+    write_meta(meta, mb)
+    for tag in ("line_indices", "match_byte_offsets", "count_lines"):
+        got = run_xsgrep(xsgrep, tag, b"Sherlock", path, ["--meta", str(meta), "--segment-bytes", "1000000", "--min-chunk", "65536"] + dev)
+        assert got == expected_output(oracle, buf, b"Sherlock", mb, tag), tag
+    err = subprocess.run([xsgrep, "--tag", "count", *dev, "Sherlock", str(path)], capture_output=True, text=True).stderr
+    assert "%d device(s)" % len(devices) in err
+
+
 def check_errors(xsgrep, tmp_path):
     out = subprocess.run([xsgrep, "abc", str(tmp_path / "missing.txt")], capture_output=True, text=True)
     assert out.returncode == 1 and "cannot open" in out.stderr
@@ -215,6 +249,15 @@ def test_extern_search_edge_files(xsgrep, tmp_path):
 @pytest.mark.gpu
 def test_extern_search_ignore_case(xsgrep, tmp_path):
     check_ignore_case(xsgrep, tmp_path)
+
+
+@pytest.mark.gpu
+def test_extern_search_multi_device(xsgrep, tmp_path):
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    check_multi_device(xsgrep, tmp_path, list(range(min(n, 4))))
 
 
 @pytest.mark.gpu

@@ -4,7 +4,7 @@ The GPU tests of tests/test_cpp_api.py and tests/test_regex.py drive `xsgrep` (t
 B200.  Everything above the C ABI is host logic -- reader threads that pread slices of the same segment, the v1 chunk
 rule applied to segments, carries across segment edges (also longer than the headroom), recycling of the pinned
 buffers, the live iterator, the regex host stage, the failure path -- and a container without a GPU can check it when
-the C ABI underneath answers: tests/cpp/xsg_testdouble.cpp implements the 17 entry points the header calls with the CPU
+the C ABI underneath answers: tests/cpp/xsg_testdouble.cpp implements the 19 entry points the header calls with the CPU
 oracle and reads every pushed segment LATE (inside the next push, like the real library's scan), comparing a checksum
 taken at push time, so a buffer recycled too early is an error and not luck.
 
@@ -136,6 +136,12 @@ def test_ignore_case(double, tmp_path):
 
 def test_errors(double, tmp_path):
     capi.check_errors(double, tmp_path)
+
+
+def test_multi_device_lanes(double, tmp_path):
+    """xs::Options::devices: the round-robin lanes, the file-order harvest and the host-side line-index bases, with
+    three pretend devices (the double accepts any device list)."""
+    capi.check_multi_device(double, tmp_path, [0, 1, 2])
 
 
 def test_regex(double, tmp_path):

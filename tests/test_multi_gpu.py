@@ -171,8 +171,11 @@ def _peer_rank_main(rank, world, port, out_dir):
         for i, pat in enumerate((b"Sherlock", b"the", b"zzzz-not-there")):
             if rank == i % world:
                 torch.cuda._sleep(200_000_000)   # one rank is late: the others must wait on the device
-            res = ctx.scan(corpus, pat, xs.MATCH_BYTE_OFFSETS | xs.LINE_INDICES | xs.COUNT_LINES, offset_base=b0)
-            ex.push()
+            # rounds alternate between the two ways to publish: from inside the scan, and with a launch of its own
+            res = ctx.scan(corpus, pat, xs.MATCH_BYTE_OFFSETS | xs.LINE_INDICES | xs.COUNT_LINES, offset_base=b0,
+                           publish=(i % 2 == 0))
+            if i % 2:
+                ex.push(res)
             ex.rebase(res)
             out["m%d" % i] = res.vector(xs.MATCH_BYTE_OFFSETS)
             out["l%d" % i] = res.vector(xs.LINE_INDICES)
@@ -218,3 +221,118 @@ def test_peer_exchange_two_gpus(tmp_path):
     import torch.multiprocessing as mp
     mp.spawn(_peer_rank_main, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
     _check_peer_outputs(str(tmp_path), 2)
+
+
+# ---- one process, several devices (xsg_init_multi) ------------------------------------------------------------------
+def _n_gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.gpu
+def test_search_host_multi_single_device_list():
+    """xsg_search_host_multi with a list of ONE device is xsg_search_host (same code path, no local line indices)."""
+    import xsearch_b200 as xs
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    mc = xs.MultiContext([0])
+    kinds = xs.COUNT_LINES | xs.LINE_INDICES | xs.MATCH_BYTE_OFFSETS | xs.LINES
+    os.environ["XSG_SEGMENT_MB"] = "1"
+    try:
+        res = mc.search_host(buf, None, b"Sherlock", kinds, bounds=bounds, line_index_base=7)
+    finally:
+        del os.environ["XSG_SEGMENT_MB"]
+    assert np.array_equal(res.vector(xs.LINE_INDICES), oracle.line_indices(buf, b"Sherlock", bounds) + np.uint64(7))
+    assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), oracle.match_byte_offsets(buf, b"Sherlock", bounds))
+    res.free()
+    mc.close()
+
+
+@pytest.mark.gpu
+def test_search_host_multi_devices():
+    """ONE host buffer, segments dealt round-robin to all devices of the box, ONE result in file order with global
+    offsets and line indices (bases added on the device, no collective): bit-identical to the oracle on the whole
+    buffer, for several segment sizes (more, as many and fewer segments than devices)."""
+    n = _n_gpus()
+    if n < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    import xsearch_b200 as xs
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    mc = xs.MultiContext(list(range(min(n, 4))))
+    kinds = xs.COUNT | xs.COUNT_LINES | xs.LINE_INDICES | xs.LINE_BYTE_OFFSETS | xs.MATCH_BYTE_OFFSETS | xs.LINES
+    for seg_mb, pat in (("1", b"Sherlock"), ("1", b"the"), ("2", b"that"), ("64", b"Sherlock")):
+        os.environ["XSG_SEGMENT_MB"] = seg_mb
+        try:
+            res = mc.search_host(buf, None, pat, kinds, bounds=bounds, offset_base=1000, line_index_base=5)
+        finally:
+            del os.environ["XSG_SEGMENT_MB"]
+        assert res.count(xs.COUNT) == oracle.count(buf, pat, bounds, False)
+        assert res.count(xs.COUNT_LINES) == oracle.count(buf, pat, bounds, True)
+        assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), oracle.match_byte_offsets(buf, pat, bounds) + np.uint64(1000))
+        assert np.array_equal(res.vector(xs.LINE_BYTE_OFFSETS), oracle.line_byte_offsets(buf, pat, bounds) + np.uint64(1000))
+        assert np.array_equal(res.vector(xs.LINE_INDICES), oracle.line_indices(buf, pat, bounds) + np.uint64(5))
+        st, ln = res.line_spans()
+        es, el = oracle.lines(buf, pat, bounds)
+        assert np.array_equal(st, es + np.uint64(1000)) and np.array_equal(ln, el)
+        assert res.newlines == int((buf == 10).sum())
+        res.free()
+    mc.close()
+
+
+@pytest.mark.gpu
+def test_local_exchange_devices():
+    """Device-resident shards on several devices of ONE process: the exchanges are connected through peer access
+    (xsg_exchange_connect_local, no IPC handles); publishing from inside the scan and with xsg_exchange_push, a
+    streamed multi-part result included; publishing twice without waiting is refused."""
+    n = _n_gpus()
+    if n < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    import xsearch_b200 as xs
+    oracle, _ = oracle_lib.load(build=False)
+    buf, bounds = _corpus()
+    world = min(n, 4)
+    mc = xs.MultiContext(list(range(world)))
+    exs = mc.exchanges()
+    shards = xs.shard_chunks(bounds, world)
+    corp, base, sb = [], [], []
+    for r, (c0, c1) in enumerate(shards):
+        b0 = int(bounds[c0 - 1]) if c0 else 0
+        b1 = int(bounds[c1 - 1]) if c1 > c0 else b0
+        base.append(b0)
+        sb.append(bounds[c0:c1] - np.uint64(b0))
+        corp.append(mc[r].corpus_from_host(buf[b0:b1], bounds=sb[-1]))
+    kinds = xs.MATCH_BYTE_OFFSETS | xs.LINE_INDICES | xs.COUNT_LINES
+    for rnd, pat in enumerate((b"Sherlock", b"the", b"zzzz-not-there")):
+        exp_m, exp_l = oracle.match_byte_offsets(buf, pat, bounds), oracle.line_indices(buf, pat, bounds)
+        res = []
+        for r in range(world):  # every rank publishes ...
+            if rnd == 1:  # ... a streamed (multi-part) result with a launch of its own
+                c0, c1 = shards[r]
+                b1 = int(bounds[c1 - 1]) if c1 > c0 else base[r]
+                os.environ["XSG_SEGMENT_MB"] = "1"
+                try:
+                    q = mc[r].search_host(buf[base[r]:b1], None, pat, kinds, bounds=sb[r], offset_base=base[r])
+                finally:
+                    del os.environ["XSG_SEGMENT_MB"]
+                exs[r].push(q)
+            else:  # ... from inside the scan
+                q = mc[r].scan(corp[r], pat, kinds, offset_base=base[r], publish=True)
+            res.append(q)
+        if rnd == 0:  # a second round before the first was waited for would overrun the slot parities
+            with pytest.raises(xs.XsgError):
+                exs[0].push(res[0])
+        for r in range(world):  # ... then every rank waits for all and fixes its line indices up
+            exs[r].rebase(res[r])
+        assert np.array_equal(np.concatenate([q.vector(xs.MATCH_BYTE_OFFSETS) for q in res]), exp_m), pat
+        assert np.array_equal(np.concatenate([q.vector(xs.LINE_INDICES) for q in res]), exp_l), pat
+        t = exs[world - 1].totals()
+        assert int(t[:, 0].sum()) == int((buf == 10).sum()) and int(t[:, 1].sum()) == exp_m.size and int(t[:, 2].sum()) == exp_l.size
+        for r in range(world):
+            exs[r].check()
+            res[r].free()
+    for e in exs:
+        e.close()
+    for c in corp:
+        c.free()
+    mc.close()

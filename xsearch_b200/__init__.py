@@ -29,6 +29,8 @@ LINE_BYTE_OFFSETS = 1 << 3
 LINE_INDICES = 1 << 4
 LINES = 1 << 5
 SCAN_IGNORE_CASE = 1  # xsg_scan_opts.flags
+SCAN_PUBLISH = 2
+SCAN_LOCAL_LINE_INDEX = 4
 
 # the reference's tag names (README.md:72-81; tests also spell xs::count as count_matches)
 TAGS = {
@@ -42,16 +44,17 @@ TAGS = {
 }
 
 EXPORTS = [
-    "xsg_last_error", "xsg_version", "xsg_init", "xsg_destroy", "xsg_device_info", "xsg_set_stream", "xsg_host_alloc",
+    "xsg_last_error", "xsg_version", "xsg_init", "xsg_init_multi", "xsg_destroy", "xsg_device_info", "xsg_set_stream", "xsg_host_alloc",
     "xsg_host_free", "xsg_corpus_alloc", "xsg_corpus_wrap", "xsg_corpus_free", "xsg_corpus_size",
     "xsg_corpus_device_ptr", "xsg_corpus_upload", "xsg_corpus_download", "xsg_corpus_fill_synth",
     "xsg_corpus_chunk", "xsg_corpus_set_bounds", "xsg_corpus_num_chunks", "xsg_corpus_get_bounds",
-    "xsg_synth_host", "xsg_chunk_bounds_host", "xsg_scan", "xsg_search_host", "xsg_stream_open", "xsg_stream_push",
+    "xsg_synth_host", "xsg_chunk_bounds_host", "xsg_scan", "xsg_search_host", "xsg_search_host_multi", "xsg_stream_open", "xsg_stream_push",
+    "xsg_stream_push_at",
     "xsg_stream_wait_copied", "xsg_stream_result", "xsg_stream_close", "xsg_stream_abort", "xsg_result_num_parts",
     "xsg_result_part_count", "xsg_result_part_newlines", "xsg_result_part_copy", "xsg_result_part_copy_line_lengths", "xsg_result_count",
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
     "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_scan_summary_device", "xsg_result_rebase_from_table", "xsg_result_free",
-    "xsg_exchange_create", "xsg_exchange_connect", "xsg_exchange_push", "xsg_result_rebase_exchanged", "xsg_exchange_totals",
+    "xsg_exchange_create", "xsg_exchange_connect", "xsg_exchange_connect_local", "xsg_exchange_check", "xsg_exchange_push", "xsg_result_rebase_exchanged", "xsg_exchange_totals",
     "xsg_exchange_destroy",
 ]
 
@@ -98,6 +101,7 @@ def _load() -> C.CDLL:
         "xsg_last_error": (C.c_char_p, []),
         "xsg_version": (i32, []),
         "xsg_init": (i32, [i32, C.POINTER(vp)]),
+        "xsg_init_multi": (i32, [C.POINTER(i32), i32, C.POINTER(vp)]),
         "xsg_destroy": (None, [vp]),
         "xsg_device_info": (i32, [vp, C.POINTER(i32), pu64, C.c_char_p, C.c_size_t]),
         "xsg_set_stream": (i32, [vp, vp]),
@@ -120,8 +124,11 @@ def _load() -> C.CDLL:
         "xsg_scan": (i32, [vp, vp, C.c_char_p, u32, u32, C.POINTER(ScanOpts), C.POINTER(vp)]),
         "xsg_search_host": (i32, [vp, vp, u64, pu64, u64, u64, C.c_char_p, u32, u32, C.POINTER(ScanOpts),
                                   C.POINTER(vp)]),
+        "xsg_search_host_multi": (i32, [C.POINTER(vp), i32, vp, u64, pu64, u64, u64, C.c_char_p, u32, u32, C.POINTER(ScanOpts),
+                                        C.POINTER(vp)]),
         "xsg_stream_open": (i32, [vp, C.c_char_p, u32, u32, C.POINTER(ScanOpts), C.POINTER(vp)]),
         "xsg_stream_push": (i32, [vp, vp, u64, pu64, u64, pu64]),
+        "xsg_stream_push_at": (i32, [vp, vp, u64, pu64, u64, u64, pu64]),
         "xsg_stream_wait_copied": (i32, [vp, u64]),
         "xsg_stream_result": (vp, [vp]),
         "xsg_stream_close": (i32, [vp, C.POINTER(vp)]),
@@ -144,7 +151,9 @@ def _load() -> C.CDLL:
         "xsg_result_free": (None, [vp]),
         "xsg_exchange_create": (i32, [vp, u32, u32, C.POINTER(vp), vp]),
         "xsg_exchange_connect": (i32, [vp, vp]),
-        "xsg_exchange_push": (i32, [vp]),
+        "xsg_exchange_connect_local": (i32, [C.POINTER(vp), u32]),
+        "xsg_exchange_check": (i32, [vp]),
+        "xsg_exchange_push": (i32, [vp, vp]),
         "xsg_result_rebase_exchanged": (i32, [vp, vp]),
         "xsg_exchange_totals": (i32, [vp, pu64]),
         "xsg_exchange_destroy": (None, [vp]),
@@ -164,8 +173,8 @@ def _check(rc: int) -> None:
         raise XsgError(rc, (lib.xsg_last_error() or b"").decode("utf-8", "replace"))
 
 
-from .api import (Context, Corpus, Result, Searcher, Stream, Exchange, extern_search, synth_host, chunk_bounds_host, pinned_empty,  # noqa: E402
+from .api import (Context, MultiContext, Corpus, Result, Searcher, Stream, Exchange, extern_search, synth_host, chunk_bounds_host, pinned_empty,  # noqa: E402
                   shard_chunks, shard_exchange, sharded_scan, sharded_scan_async)
 
-__all__ = ["Context", "Corpus", "Result", "Searcher", "Stream", "Exchange", "extern_search", "synth_host", "chunk_bounds_host", "pinned_empty",
+__all__ = ["Context", "MultiContext", "Corpus", "Result", "Searcher", "Stream", "Exchange", "extern_search", "synth_host", "chunk_bounds_host", "pinned_empty",
            "shard_chunks", "shard_exchange", "sharded_scan", "sharded_scan_async", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]

@@ -16,7 +16,7 @@ from typing import Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from . import (SCAN_IGNORE_CASE, COUNT, COUNT_LINES, DEFAULT_MIN_CHUNK, LINE_BYTE_OFFSETS, LINE_INDICES, LINES,
+from . import (SCAN_IGNORE_CASE, SCAN_PUBLISH, COUNT, COUNT_LINES, DEFAULT_MIN_CHUNK, LINE_BYTE_OFFSETS, LINE_INDICES, LINES,
                MATCH_BYTE_OFFSETS, SYNTH_BLOCK, TAGS, ScanOpts, SynthParams, Timings, XsgError, _check, lib)
 
 _PU64 = C.POINTER(C.c_uint64)
@@ -139,8 +139,11 @@ class Context:
 
     # -- searches ---------------------------------------------------------------------------
     def scan(self, corpus: "Corpus", pattern: bytes, kinds: int, offset_base: int = 0, line_index_base: int = 0,
-             occ_capacity: int = 0, ignore_case: bool = False) -> "Result":
-        opts = ScanOpts(offset_base, line_index_base, occ_capacity, SCAN_IGNORE_CASE if ignore_case else 0, 0)
+             occ_capacity: int = 0, ignore_case: bool = False, publish: bool = False) -> "Result":
+        """publish: the scan's last kernel also publishes the scan's summary through the Exchange attached to this
+        context (XSG_SCAN_PUBLISH) -- the push of that round without a launch of its own."""
+        flags = (SCAN_IGNORE_CASE if ignore_case else 0) | (SCAN_PUBLISH if publish else 0)
+        opts = ScanOpts(offset_base, line_index_base, occ_capacity, flags, 0)
         h = C.c_void_p()
         _check(lib.xsg_scan(self._h, corpus._h, pattern, len(pattern), kinds, C.byref(opts), C.byref(h)))
         return Result(h, kinds, self)
@@ -159,6 +162,52 @@ class Context:
         _check(lib.xsg_search_host(self._h, C.c_void_p(addr), n, bp, nb, min_chunk, pattern, len(pattern), kinds,
                                    C.byref(opts), C.byref(h)))
         return Result(h, kinds, self)
+
+
+class MultiContext:
+    """One host process, several devices (xsg_init_multi): a list of Contexts with peer access between them.
+    ``search_host`` deals the segments of ONE host buffer round-robin to the devices and returns ONE result in file
+    order (xsg_search_host_multi); ``exchanges()`` connects one Exchange per context without IPC handles."""
+
+    def __init__(self, devices: Sequence[int]):
+        n = len(devices)
+        devs = (C.c_int * n)(*devices)
+        hs = (C.c_void_p * n)()
+        _check(lib.xsg_init_multi(devs, n, hs))
+        self.contexts = []
+        for d, h in zip(devices, hs):
+            c = Context.__new__(Context)
+            c._h, c.device = C.c_void_p(h), d
+            self.contexts.append(c)
+
+    def __len__(self) -> int:
+        return len(self.contexts)
+
+    def __getitem__(self, i: int) -> "Context":
+        return self.contexts[i]
+
+    def search_host(self, buf, n_bytes: Optional[int], pattern: bytes, kinds: int, bounds: Optional[np.ndarray] = None,
+                    min_chunk: int = DEFAULT_MIN_CHUNK, offset_base: int = 0, line_index_base: int = 0,
+                    ignore_case: bool = False) -> "Result":
+        if isinstance(buf, np.ndarray):
+            addr, n = buf.ctypes.data, int(buf.size)
+        else:
+            addr, n = int(buf), int(n_bytes)
+        opts = ScanOpts(offset_base, line_index_base, 0, SCAN_IGNORE_CASE if ignore_case else 0, 0)
+        hs = (C.c_void_p * len(self.contexts))(*[c._h for c in self.contexts])
+        h = C.c_void_p()
+        bp, nb = (None, 0) if bounds is None else (_u64ptr(bounds), int(bounds.size))
+        _check(lib.xsg_search_host_multi(hs, len(self.contexts), C.c_void_p(addr), n, bp, nb, min_chunk, pattern,
+                                         len(pattern), kinds, C.byref(opts), C.byref(h)))
+        return Result(h, kinds, self.contexts[0])
+
+    def exchanges(self) -> List["Exchange"]:
+        """One connected Exchange per context (rank = position in the device list), reached through peer access."""
+        return Exchange.local(self.contexts)
+
+    def close(self) -> None:
+        for c in self.contexts:
+            c.close()
 
 
 class Stream:
@@ -461,15 +510,23 @@ def shard_exchange(newlines: int, counts: Sequence[int], group=None) -> Tuple[in
 
 
 class Exchange:
-    """The shard exchange of a multi-GPU search over NVLink peer memory (xsg_exchange, include/xsg.h): after a
-    scan, ``push()`` writes the shard summary into every rank's table with one small kernel, ``rebase(result)``
-    launches the fix-up kernel that waits for all ranks on the device and adds the lower shards' newline counts
-    to the line indices.  Only the 64-byte IPC handles travel through torch.distributed, once."""
+    """The shard exchange of a multi-GPU search over NVLink peer memory (xsg_exchange, include/xsg.h).  Per round:
+    the summary of the rank's shard is published into every rank's table -- by the scan itself
+    (``ctx.scan(..., publish=True)``, no extra launch) or by ``push(result)`` -- and ``rebase(result)`` launches the
+    fix-up kernel that waits for all ranks on the device and adds the lower shards' newline counts to the line
+    indices.  One process per GPU: only the 64-byte IPC handles travel through torch.distributed, once.  Several
+    contexts in one process: ``Exchange.local(contexts)``."""
 
-    def __init__(self, ctx: "Context", group=None):
+    def __init__(self, ctx: "Context", group=None, _local=None):
+        self.ctx = ctx
+        if _local is not None:  # one of the exchanges of Exchange.local()
+            self.world, self.rank = _local
+            h = C.c_void_p()
+            _check(lib.xsg_exchange_create(ctx._h, self.world, self.rank, C.byref(h), None))
+            self._h = h
+            return
         import torch
         import torch.distributed as dist
-        self.ctx = ctx
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         h = C.c_void_p()
         mine = (C.c_ubyte * 64)()
@@ -483,8 +540,18 @@ class Exchange:
         _check(lib.xsg_exchange_connect(self._h, C.cast(C.create_string_buffer(raw, len(raw)), C.c_void_p)))
         dist.barrier(group)  # every rank has mapped every table before the first push
 
-    def push(self) -> None:
-        _check(lib.xsg_exchange_push(self._h))
+    @staticmethod
+    def local(contexts: Sequence["Context"]) -> List["Exchange"]:
+        """All ranks in this process: contexts[r] is rank r (xsg_exchange_connect_local, peer access)."""
+        n = len(contexts)
+        exs = [Exchange(c, _local=(n, r)) for r, c in enumerate(contexts)]
+        hs = (C.c_void_p * n)(*[e._h for e in exs])
+        _check(lib.xsg_exchange_connect_local(hs, n))
+        return exs
+
+    def push(self, res: "Result") -> None:
+        """Publish the totals of a finished result (any number of parts) as this rank's summary of the next round."""
+        _check(lib.xsg_exchange_push(self._h, res._h))
 
     def rebase(self, res: "Result") -> None:
         _check(lib.xsg_result_rebase_exchanged(res._h, self._h))
@@ -494,6 +561,10 @@ class Exchange:
         out = np.empty(self.world * 4, dtype=np.uint64)
         _check(lib.xsg_exchange_totals(self._h, _u64ptr(out)))
         return out.reshape(self.world, 4)
+
+    def check(self) -> None:
+        """Raises if a wait of this exchange timed out (a peer never published)."""
+        _check(lib.xsg_exchange_check(self._h))
 
     def close(self) -> None:
         if self._h:

@@ -2,7 +2,8 @@
 // example/grep.cpp:66-80 and checkit.cpp).  Also the driver of the C++ API tests (tests/test_cpp_api.py).
 //
 //   xsgrep [--tag lines|count|count_lines|match_byte_offsets|line_byte_offsets|line_indices] [--meta FILE]
-//          [-j N] [--readers N] [--reader pread|mmap] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D] [--live]
+//          [-j N] [--readers N] [--reader pread|mmap] [--min-chunk BYTES] [--segment-bytes BYTES] [--device D]
+//          [--devices D0,D1,...] [--live]
 //          [-i] [-E | -F]
 //          PATTERN FILE
 //   -E / -F read PATTERN as a regular expression / as plain text; default: the reference's rule (utils.h:17-24).
@@ -74,9 +75,9 @@ int run(const Args& a) {
     return 2;
   }
   const xsg_timings t = searcher->timings();
-  std::fprintf(stderr, "xsgrep: %llu bytes, pipeline %.1f ms (%.2f GB/s), device scans %.2f ms, %u kernel launches\n",
+  std::fprintf(stderr, "xsgrep: %llu bytes, pipeline %.1f ms (%.2f GB/s), device scans %.2f ms, %u kernel launches, %zu device(s), pinned alloc %.1f ms\n",
                (unsigned long long)searcher->bytes(), t.h2d_ms, t.h2d_ms > 0 ? searcher->bytes() / t.h2d_ms / 1e6 : 0.0,
-               t.scan_ms, t.kernel_launches);
+               t.scan_ms, t.kernel_launches, searcher->num_devices(), searcher->pinned_alloc_ms());
   return 0;
 }
 
@@ -225,6 +226,16 @@ int main(int argc, char** argv) {
     else if (s == "--min-chunk") a.opt.min_chunk = std::strtoull(next().c_str(), nullptr, 10);
     else if (s == "--segment-bytes") a.opt.segment_bytes = std::strtoull(next().c_str(), nullptr, 10);
     else if (s == "--device") a.opt.device = std::atoi(next().c_str());
+    else if (s == "--devices") {  // one Searcher over several devices: --devices 0,1,2,3
+      a.opt.devices.clear();
+      const std::string list = next();
+      for (size_t p = 0; p < list.size();) {
+        const size_t q = list.find(',', p);
+        a.opt.devices.push_back(std::atoi(list.substr(p, q == std::string::npos ? q : q - p).c_str()));
+        if (q == std::string::npos) break;
+        p = q + 1;
+      }
+    }
     else if (s == "--reader") {
       const std::string m = next();
       if (m != "pread" && m != "mmap") {

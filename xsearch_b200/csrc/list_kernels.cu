@@ -225,12 +225,30 @@ __global__ void __launch_bounds__(256) overlap_check_kernel(const uint64_t* __re
   if (seen) *flag = 1u;
 }
 
-__global__ void summary_kernel(const DevScalars* __restrict__ d, int mode, int want_lines, unsigned long long* out) {
+// Thread 0 writes the summary of the scan; with an exchange attached (pub.world != 0) thread p < world also stores it
+// into rank p's table over peer memory and releases the round number -- the push of the shard exchange costs no
+// launch of its own.  A pass that will be redone (the list-free count saw overlapping occurrences; the direct path
+// saw tail drops or overlaps) publishes nothing: the summary of the fall-back pass does.
+__global__ void __launch_bounds__(kMaxWorld) summary_kernel(const DevScalars* __restrict__ d, int mode, int want_lines,
+                                                           unsigned long long* out, const __grid_constant__ ExPublish pub) {
   pdl_wait();
-  out[0] = d->nl_total;
-  out[1] = mode == 1 ? d->occ_total - d->zone_sub + d->zone_add : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
-  out[2] = d->sel_total[1];
-  out[3] = want_lines ? d->sel_total[1] - (d->unterminated ? 1 : 0) : 0;
+  pdl_trigger();
+  unsigned long long v[4];
+  v[0] = d->nl_total;
+  v[1] = mode == 1 ? d->occ_total - d->zone_sub + d->zone_add : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
+  v[2] = d->sel_total[1];
+  v[3] = want_lines ? d->sel_total[1] - (d->unterminated ? 1 : 0) : 0;
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) out[i] = v[i];
+  }
+  const bool redo = (mode == 1 && d->overlap != 0) || (mode == 2 && (d->drops != 0 || d->overlap != 0));
+  if (threadIdx.x < pub.world && !redo) {
+    ExSlot* slot = pub.peers.table[threadIdx.x] + (pub.round & 1) * pub.world + pub.rank;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) slot->v[i] = v[i];
+    st_release_sys(&slot->seq, pub.round);  // orders the four stores above before the round number, system-wide
+  }
 }
 
 }  // namespace
@@ -241,8 +259,12 @@ void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned 
   launch_dependent(overlap_check_kernel, dim3((unsigned)(want < 148 * 16 ? want : 148 * 16)), dim3(256), s, occ, k, m, flag);
 }
 
-void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, cudaStream_t s) {
-  launch_dependent(summary_kernel, dim3(1), dim3(1), s, static_cast<const DevScalars*>(dev_scalars), mode, want_lines, summary);
+void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, const ExPublish* pub,
+                    cudaStream_t s) {
+  static const ExPublish none = {};
+  const ExPublish& p = pub ? *pub : none;
+  launch_dependent(summary_kernel, dim3(1), dim3(p.world ? kMaxWorld : 1), s, static_cast<const DevScalars*>(dev_scalars), mode,
+                   want_lines, summary, p);
 }
 
 void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, uint32_t stride, uint32_t rank,

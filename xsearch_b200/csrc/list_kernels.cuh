@@ -68,6 +68,9 @@ void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, u
                                cudaStream_t s);
 // summary[0..4) = {newlines, matches, matching lines, lines} from the scan's device scalars
 // mode 0: list path, 1: count-only path (occ_total - zone_sub + zone_add), 2: direct path (occ_total - drops)
-void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, cudaStream_t s);
+// pub (may be nullptr): the kernel also stores the summary into every rank's exchange table and releases the round
+// (xsg_exchange.cu) -- unless a fall-back pass will follow (overlap seen / tail drops), whose summary publishes instead
+void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, const ExPublish* pub,
+                    cudaStream_t s);
 
 }  // namespace xsg

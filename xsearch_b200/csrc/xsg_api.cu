@@ -59,6 +59,41 @@ const char* xsg_last_error(void) { return g_error.c_str(); }
 int xsg_version(void) { return 1; }
 
 // ---- context ----------------------------------------------------------------------------------
+// everything xsg_init allocates; any failure leaves a partially built context that xsg_destroy takes apart
+static int init_ctx(xsg_ctx* c, int device) {
+  c->device = device;
+  XSG_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+  XSG_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  XSG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  for (auto& ev : c->ev) XSG_CUDA(cudaEventCreate(&ev));
+  for (int i = 0; i < 2; ++i) {
+    XSG_CUDA(cudaEventCreateWithFlags(&c->stage_copied[i], cudaEventDisableTiming));
+    XSG_CUDA(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
+  }
+  XSG_CUDA(cudaMalloc(&c->d_scalars, sizeof(DevScalars)));
+  XSG_CUDA(cudaMalloc(&c->d_summary, 4 * sizeof(unsigned long long)));
+  XSG_CUDA(cudaMemset(c->d_summary, 0, 4 * sizeof(unsigned long long)));
+  XSG_CUDA(cudaHostAlloc(&c->h_scalars, sizeof(DevScalars), cudaHostAllocDefault));
+  XSG_CUDA(cudaMalloc(&c->d_konst, 12 * sizeof(uint32_t)));
+  XSG_CUDA(cudaHostAlloc(&c->h_konst, 12 * sizeof(uint32_t), cudaHostAllocDefault));
+  XSG_CUDA(cudaHostAlloc(&c->h_ex_bad, sizeof(unsigned int), cudaHostAllocMapped));
+  *c->h_ex_bad = 0;
+  XSG_CUDA(cudaHostGetDevicePointer(&c->d_ex_bad, c->h_ex_bad, 0));
+  // result vectors come from a stream-ordered pool of the context's OWN (freed memory stays in it instead of going
+  // back to the driver); the device's default pool -- shared with every other cudaMallocAsync user of the process --
+  // is left as it is
+  cudaMemPoolProps props = {};
+  props.allocType = cudaMemAllocationTypePinned;
+  props.handleTypes = cudaMemHandleTypeNone;
+  props.location.type = cudaMemLocationTypeDevice;
+  props.location.id = device;
+  XSG_CUDA(cudaMemPoolCreate(&c->pool, &props));
+  unsigned long long thr = ~0ull;
+  XSG_CUDA(cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  return XSG_OK;
+}
+
 int xsg_init(int device, xsg_ctx** out) {
   if (!out) return XSG_ERR_ARG;
   *out = nullptr;
@@ -77,53 +112,77 @@ int xsg_init(int device, xsg_ctx** out) {
   XSG_CUDA(cudaSetDevice(device));
   xsg_ctx* c = new (std::nothrow) xsg_ctx();
   if (!c) return XSG_ERR_NOMEM;
-  c->device = device;
-  XSG_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
-  XSG_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
-  c->stream = c->own_stream;
-  XSG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-  for (auto& ev : c->ev) XSG_CUDA(cudaEventCreate(&ev));
-  for (int i = 0; i < 2; ++i) {
-    XSG_CUDA(cudaEventCreateWithFlags(&c->stage_copied[i], cudaEventDisableTiming));
-    XSG_CUDA(cudaEventCreateWithFlags(&c->stage_free[i], cudaEventDisableTiming));
-  }
-  XSG_CUDA(cudaMalloc(&c->d_scalars, sizeof(DevScalars)));
-  XSG_CUDA(cudaMalloc(&c->d_summary, 4 * sizeof(unsigned long long)));
-  XSG_CUDA(cudaMemset(c->d_summary, 0, 4 * sizeof(unsigned long long)));
-  XSG_CUDA(cudaHostAlloc(&c->h_scalars, sizeof(DevScalars), cudaHostAllocDefault));
-  XSG_CUDA(cudaMalloc(&c->d_konst, 12 * sizeof(uint32_t)));
-  XSG_CUDA(cudaHostAlloc(&c->h_konst, 12 * sizeof(uint32_t), cudaHostAllocDefault));
-  // keep freed result memory in the stream-ordered pool instead of returning it to the driver
-  cudaMemPool_t pool;
-  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-    unsigned long long thr = ~0ull;
-    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  const int rc = init_ctx(c, device);
+  if (rc != XSG_OK) {
+    const std::string why = g_error;  // xsg_destroy's own CUDA calls must not overwrite the reason
+    c->device = device;
+    xsg_destroy(c);
+    cudaGetLastError();
+    g_error = why;
+    return rc;
   }
   *out = c;
+  return XSG_OK;
+}
+
+// One host process, several devices (xsg_init(const int* devs, int n, ...)): n contexts, one per
+// device, with peer access enabled between all pairs that support it (for xsg_exchange_connect_local).  On failure
+// nothing is left behind.
+int xsg_init_multi(const int* devices, int n, xsg_ctx** out) {
+  if (!devices || !out || n <= 0) return XSG_ERR_ARG;
+  for (int i = 0; i < n; ++i) out[i] = nullptr;
+  for (int i = 0; i < n; ++i) {
+    for (int j = 0; j < i; ++j)
+      if (devices[i] == devices[j]) {
+        set_error("xsg_init_multi: a device is listed twice");
+        for (int k = 0; k < i; ++k) xsg_destroy(out[k]), out[k] = nullptr;
+        return XSG_ERR_ARG;
+      }
+    const int rc = xsg_init(devices[i], &out[i]);
+    if (rc != XSG_OK) {
+      const std::string why = g_error;
+      for (int k = 0; k < i; ++k) xsg_destroy(out[k]), out[k] = nullptr;
+      g_error = why;
+      return rc;
+    }
+  }
+  for (int i = 0; i < n; ++i) {
+    cudaSetDevice(devices[i]);
+    for (int j = 0; j < n; ++j) {
+      int can = 0;
+      if (i == j || cudaDeviceCanAccessPeer(&can, devices[i], devices[j]) != cudaSuccess || !can) continue;
+      cudaDeviceEnablePeerAccess(devices[j], 0);  // "already enabled" is fine
+      cudaGetLastError();
+    }
+  }
   return XSG_OK;
 }
 
 void xsg_destroy(xsg_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  cudaStreamSynchronize(c->stream);
-  cudaStreamSynchronize(c->copy_stream);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
   Scratch* all[] = {&c->gran_count, &c->gran_prefix, &c->nl_granule, &c->nl_prefix, &c->scan_tmp, &c->occ,
                     &c->sel, &c->desc2, &c->selq, &c->gran_mask, &c->gran_first, &c->stage[0], &c->stage[1], &c->seg_bounds, &c->stage_bounds[0],
                     &c->stage_bounds[1]};
   for (Scratch* s : all) s->release();
-  for (auto& ev : c->ev) cudaEventDestroy(ev);
+  for (auto& ev : c->ev)
+    if (ev) cudaEventDestroy(ev);
   for (int i = 0; i < 2; ++i) {
-    cudaEventDestroy(c->stage_copied[i]);
-    cudaEventDestroy(c->stage_free[i]);
+    if (c->stage_copied[i]) cudaEventDestroy(c->stage_copied[i]);
+    if (c->stage_free[i]) cudaEventDestroy(c->stage_free[i]);
   }
-  cudaFree(c->d_scalars);
-  cudaFree(c->d_summary);
-  cudaFreeHost(c->h_scalars);
-  cudaFree(c->d_konst);
-  cudaFreeHost(c->h_konst);
-  cudaStreamDestroy(c->own_stream);
-  cudaStreamDestroy(c->copy_stream);
+  if (c->d_scalars) cudaFree(c->d_scalars);
+  if (c->d_summary) cudaFree(c->d_summary);
+  if (c->h_scalars) cudaFreeHost(c->h_scalars);
+  if (c->d_konst) cudaFree(c->d_konst);
+  if (c->h_konst) cudaFreeHost(c->h_konst);
+  if (c->h_ex_bad) cudaFreeHost(c->h_ex_bad);
+  if (c->pool) cudaMemPoolDestroy(c->pool);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  cudaGetLastError();
   delete c;
 }
 

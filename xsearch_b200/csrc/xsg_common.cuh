@@ -100,6 +100,26 @@ struct DevScalars {
   unsigned int ticket[5];  // tile counters: [0], [1] the two prefix-sum tables, [2], [3] compaction (match / line family)
   unsigned int overlap;    // count_kernel<.., OVL>: some pair of occurrences overlaps (bordered patterns)
 };
+// ---- shard exchange over peer memory (xsg_exchange.cu) ----------------------------------------------
+// One 64-byte slot per (parity, source rank) in every rank's table; a source rank stores its 4-word scan
+// summary, then releases the round number system-wide.
+struct ExSlot {
+  unsigned long long v[4];  // {newlines, matches, matching lines, lines}
+  unsigned long long seq;   // round number, written last (st.release.sys)
+  unsigned long long pad[3];
+};
+static_assert(sizeof(ExSlot) == 64, "one slot per 64-byte line");
+constexpr int kMaxWorld = 64;
+struct ExPeers {
+  ExSlot* table[kMaxWorld];  // [rank] -> that rank's slots[2][world] (own memory, IPC mapping or peer mapping)
+};
+// what summary_kernel needs to publish a scan's summary itself (world == 0: nothing to publish)
+struct ExPublish {
+  ExPeers peers;
+  uint32_t world, rank;
+  unsigned long long round;
+};
+
 // small helpers usable from host code
 
 inline uint64_t div_up(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
@@ -114,6 +134,14 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
 }
 __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 // streaming 16-byte load: read-only path, do not allocate in L1 (each byte is read once)
 __device__ __forceinline__ uint4 ld_stream_v4(const uint4* p) {

@@ -30,6 +30,8 @@ struct Scratch {
 
 }  // namespace xsg
 
+struct xsg_exchange;
+
 struct xsg_ctx {
   int device = 0;
   int sm_count = 0;
@@ -37,6 +39,7 @@ struct xsg_ctx {
   cudaStream_t own_stream = nullptr;
   cudaStream_t copy_stream = nullptr;  // H2D of streamed segments
   cudaEvent_t ev[6] = {};
+  cudaMemPool_t pool = nullptr;        // stream-ordered pool of this context: result vectors
   xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2, selq, gran_mask, gran_first;
   xsg::Scratch stage[2];               // streamed segments (double buffer)
   xsg::Scratch seg_bounds;
@@ -49,6 +52,22 @@ struct xsg_ctx {
   uint32_t* h_konst = nullptr;           // pinned staging of the same (= what d_konst holds once konst_valid)
   bool konst_valid = false;
   uint32_t epoch = 0;                    // tag of the look-back descriptors of the next launch (xsg::lookback)
+  xsg_exchange* exchange = nullptr;      // the shard exchange attached to this context (xsg_exchange_create), if any
+  unsigned int* h_ex_bad = nullptr;      // mapped pinned flag: a wait of the exchange timed out (set by kernels)
+  unsigned int* d_ex_bad = nullptr;      // the same word as the device sees it
+};
+
+struct xsg_exchange {
+  xsg_ctx* ctx = nullptr;
+  uint32_t world = 0, rank = 0;
+  unsigned long long round = 0;         // last round published by this rank
+  unsigned long long waited = 0;        // last round this rank waited for (rebase / totals)
+  xsg::ExSlot* local = nullptr;         // slots[2][world], written by the peers
+  xsg::ExPeers peers = {};
+  std::vector<void*> opened;            // IPC mappings to close
+  unsigned long long* d_out = nullptr;  // [world * 4] gathered table for xsg_exchange_totals
+  unsigned long long* h_out = nullptr;  // pinned [world * 4]
+  bool connected = false;
 };
 
 struct xsg_corpus {
@@ -61,6 +80,7 @@ struct xsg_corpus {
 };
 
 struct xsg_part {  // results of one device-resident scan (one streamed segment)
+  xsg_ctx* ctx = nullptr;  // the context (device, stream, pool) its vectors live in
   uint64_t* match_off = nullptr;
   uint64_t* line_off = nullptr;
   uint64_t* line_idx = nullptr;
@@ -73,6 +93,8 @@ struct xsg_part {  // results of one device-resident scan (one streamed segment)
 };
 
 namespace xsg {
+int exchange_begin_round(xsg_ctx* ctx, ExPublish* pub);  // xsg_exchange.cu
+int exchange_check_flag(xsg_ctx* ctx);
 struct ScanStats {
   uint64_t newlines = 0, raw = 0;
   float main_ms = 0, post_ms = 0, scan_ms = 0;
@@ -87,6 +109,7 @@ struct xsg_result {
   uint64_t count = 0, count_lines = 0, n_lines = 0;
   uint64_t newlines = 0, raw_occurrences = 0;
   xsg_timings timings = {};
+  bool exchanged = false;  // line indices were fixed up by xsg_result_rebase_exchanged: copies report a timed-out wait
   // lazily concatenated device copies for xsg_result_device_ptr on multi-part results
   uint64_t* concat[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
@@ -96,6 +119,7 @@ struct xsg_stream {
   xsg::Pattern pat;
   uint32_t kinds = 0;
   uint64_t goff_base = 0, lidx = 0, occ_cap = 0;
+  bool local_lidx = false;    // XSG_SCAN_LOCAL_LINE_INDEX: every part numbers its lines from its own first byte
   xsg_result* res = nullptr;
   xsg::ScanStats st;
   uint64_t pushed = 0;        // segments pushed so far (ticket of the next one)

@@ -110,6 +110,8 @@ int make_pattern(const uint8_t* p_in, uint32_t m, bool icase, Pattern* out) {
 }
 
 void free_part(xsg_ctx* ctx, xsg_part& p) {
+  if (p.ctx) ctx = p.ctx;  // a result of a multi-device search holds parts of several contexts
+  cudaSetDevice(ctx->device);
   uint64_t** arrs[] = {&p.match_off, &p.line_off, &p.line_idx, &p.line_start, &p.line_len};
   for (uint64_t** a : arrs) {
     if (*a) cudaFreeAsync(*a, ctx->stream);
@@ -119,7 +121,7 @@ void free_part(xsg_ctx* ctx, xsg_part& p) {
 
 int alloc_out(xsg_ctx* ctx, uint64_t** p, uint64_t entries) {
   *p = nullptr;
-  XSG_CUDA(cudaMallocAsync(p, std::max<uint64_t>(entries, 1) * sizeof(uint64_t), ctx->stream));
+  XSG_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void**>(p), std::max<uint64_t>(entries, 1) * sizeof(uint64_t), ctx->pool, ctx->stream));
   return XSG_OK;
 }
 
@@ -165,13 +167,15 @@ int read_scalars(xsg_ctx* ctx) {
 // One device-resident scan of buf[0..n) with reference chunks d_bounds[0..nb).
 int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_bounds, uint64_t nb,
                 const Pattern& pat, uint32_t kinds, uint64_t goff, uint64_t lidx_base, uint64_t occ_cap_opt,
-                xsg_part* part, ScanStats* st) {
+                xsg_part* part, ScanStats* st, const ExPublish* pub = nullptr) {
   cudaStream_t s = ctx->stream;
   *part = xsg_part();
+  part->ctx = ctx;
   XSG_CUDA(cudaEventRecord(ctx->ev[0], s));
   XSG_CUDA(cudaMemsetAsync(ctx->d_scalars, 0, sizeof(DevScalars), s));
   if (n == 0 || nb == 0) {
-    XSG_CUDA(cudaMemsetAsync(ctx->d_summary, 0, 4 * sizeof(unsigned long long), s));
+    launch_summary(ctx->d_scalars, 0, 0, ctx->d_summary, pub, s);  // all zero (and published, if an exchange wants it)
+    XSG_CUDA(cudaGetLastError());
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     XSG_CUDA(cudaStreamSynchronize(s));
     return XSG_OK;
@@ -213,7 +217,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     launch_reduce_u32(a.gran_count, n_gran, &ds->occ_total, s);
     launch_zone_count(buf, n, d_bounds, nb, pat, a.gran_count, &ds->zone_sub, &ds->zone_add, s);
     XSG_CUDA(cudaGetLastError());
-    launch_summary(ds, 1, 0, ctx->d_summary, s);
+    launch_summary(ds, 1, 0, ctx->d_summary, pub, s);
     st->launches += 3 + (pat.m > 1 ? 1 : 0);
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
@@ -360,7 +364,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         st->launches += c.selq ? 2 : 1;
       }
     }
-    launch_summary(ds, direct ? 2 : 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, s);
+    launch_summary(ds, direct ? 2 : 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s);
     st->launches += 1;
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
@@ -385,7 +389,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       c.unterminated = &ds->unterminated;
       launch_compact(c, pat, s);
       XSG_CUDA(cudaGetLastError());
-      launch_summary(ds, 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, s);
+      launch_summary(ds, 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s);
       st->launches += 4;
       XSG_CUDA(cudaFreeAsync(part->match_off, s));
       part->match_off = fixed;
