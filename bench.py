@@ -84,6 +84,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-resident", action="store_true",
                     help="skip the device-resident leg (value is then the e2e number; for shards larger than HBM)")
+    ap.add_argument("--single-process", action="store_true",
+                    help="N > 1: rank 0 alone drives all N devices through xsg_search_host_multi (one Searcher over N "
+                         "devices: segments of ONE pinned host buffer dealt round-robin, one result in file order); the "
+                         "other ranks idle.  Host-streamed only: value is the e2e number")
     ap.add_argument("--exchange", choices=["p2p", "nccl"], default="p2p",
                     help="N > 1: shard summaries over NVLink peer memory (own kernels) or an NCCL all-gather")
     ap.add_argument("--no-cpu", action="store_true", help="skip the reference run: no parity block, no cpu_baseline")
@@ -713,10 +717,158 @@ def run_ours(args):
         raise SystemExit("bench.py: %d result elements differ from the reference" % parity["mismatches"])
 
 
+def run_single_process(args):
+    """--single-process: ONE host process, N devices, one logical file in one pinned buffer (the reference's data-parallel
+    unit is num_threads workers inside one Searcher, include/xsearch/Searcher.h:141-145; this is its GPU analogue).
+    Under torchrun the ranks > 0 only keep the barriers company."""
+    import torch
+    import torch.distributed as dist
+
+    import xsearch_b200 as xs
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    ndev = args.gpus
+    torch.cuda.set_device(local)
+    if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    tags, pat, needle, rate, seed, nbytes, scaling = workload_spec(args, ndev)
+    total = nbytes * ndev
+    kinds = 0
+    for t in tags:
+        kinds |= xs.TAGS[t]
+    line = None
+    bad = 0
+    if rank == 0:
+        mc = xs.MultiContext(list(range(ndev)))
+        hp = C.c_void_p()
+        xs._check(xs.lib.xsg_host_alloc(total, C.byref(hp)))
+        params = xs.SynthParams.make(seed, needle, rate)
+        nblk = nbytes // xs.SYNTH_BLOCK
+        all_bounds = []
+        for d in range(ndev):  # every device generates its share of the file, which then lives in host memory only
+            c = mc[d].corpus(nbytes)
+            c.fill_synth(params, first_block=d * nblk)
+            c.chunk()
+            all_bounds.append(c.bounds() + np.uint64(d * nbytes))
+            xs._check(xs.lib.xsg_corpus_download(c._h, C.c_void_p(hp.value + d * nbytes), 0, nbytes))
+            c.free()
+        bounds = np.concatenate(all_bounds)
+        pinned_out = {}
+
+        def pinned_vec(name, need):
+            if name not in pinned_out or pinned_out[name].size < need:
+                pinned_out[name] = xs.pinned_empty(need + need // 8 + 1024)
+            return pinned_out[name]
+
+        def step():
+            r = mc.search_host(hp.value, total, pat, kinds, bounds=bounds)
+            got, out = 8, {}
+            for t in tags:
+                k = xs.TAGS[t]
+                if k in (xs.COUNT, xs.COUNT_LINES):
+                    out[t] = r.count(k)
+                    continue
+                need = r.count(k)
+                v = r.vector(k, out=pinned_vec(t, need))
+                got += v.nbytes
+                if k == xs.LINES:
+                    ln = pinned_vec(t + "/len", need)[:need]
+                    if need:
+                        xs._check(xs.lib.xsg_result_copy_line_lengths(r._h, ln.ctypes.data_as(_PU64), need))
+                    got += ln.nbytes
+                    v = (v, ln)
+                out[t] = v
+            tm = r.timings()
+            r.free()
+            return got, out, tm.kernel_launches
+
+        for _ in range(min(2, args.warmup)):
+            step()
+        ksteps = args.e2e_steps or min(args.steps, 6)
+        sampler = ClockSampler(0, args.clock_interval_ms)
+        sampler.start()
+        launches = 0
+        t0 = time.perf_counter()
+        for _ in range(ksteps):
+            d2h, streamed, nl = step()  # host-synchronous: the result vectors are on the host when it returns
+            launches += nl
+        dt = time.perf_counter() - t0
+        clocks = sampler.stop()
+        # denominator: plain H2D of the same pinned bytes, every device its share, all at once (one thread per device)
+        dst = [mc[d].corpus(nbytes) for d in range(ndev)]
+
+        def plain(d):
+            xs._check(xs.lib.xsg_corpus_upload(dst[d]._h, C.c_void_p(hp.value + d * nbytes), 0, nbytes))
+        best = None
+        for _ in range(2):
+            th = [threading.Thread(target=plain, args=(d,)) for d in range(ndev)]
+            p0 = time.perf_counter()
+            [t.start() for t in th]
+            [t.join() for t in th]
+            pdt = time.perf_counter() - p0
+            best = pdt if best is None or pdt < best else best
+        for c in dst:
+            c.free()
+        value = total * ksteps / dt / 1e9
+        h2d_peak = total / best / 1e9
+        parity = cpu = None
+        if not args.no_cpu:
+            cores = os.cpu_count() or 1
+            chk = CpuChecker()
+            cnt = max([int(v[0].size) if isinstance(v, tuple) else (int(v.size) if not isinstance(v, int) else v)
+                       for v in streamed.values()] + [0])
+            c0 = time.perf_counter()
+            exp = chk.run_tags(tags, hp.value, total, pat, bounds, cores, max(1 << 20, cnt + cnt // 8 + 1024))
+            cdt = time.perf_counter() - c0
+            bad, checked = compare_outputs(tags, streamed, exp, 0, 0)
+            parity = {"oracle": chk.kind, "checked_bytes": int(total), "checked_bytes_total": int(total), "tags": list(tags),
+                      "legs": ["host-streamed, %d devices, one process" % ndev], "elements_compared": int(checked),
+                      "mismatches": int(bad), "ranks": 1,
+                      "how": "the reference's wrappers over ALL bytes of the file (same v1 chunks), vectors compared element by "
+                             "element with the merged result of the %d devices" % ndev}
+            cpu = {"value": round(total / cdt / 1e9, 3), "unit": "GB/s", "cores": cores, "kind": chk.kind,
+                   "sample": "all %.2f GB of the file, one pass, all requested tags" % (total / 1e9)}
+        line = {
+            "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": ndev, "steps": ksteps, "warmup": min(2, args.warmup),
+            "ms_per_step": round(dt / ksteps * 1e3, 3), "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {**config_of(args, pat, tags, nbytes, scaling, ndev), "parallelism": "one process x %d devices" % ndev},
+            "results": {"global_results": int(result_count(streamed[tags[-1]]) if isinstance(streamed[tags[-1]], int)
+                                             else (streamed[tags[-1]][0].size if isinstance(streamed[tags[-1]], tuple)
+                                                   else streamed[tags[-1]].size)),
+                        "reference_chunks": int(bounds.size)},
+            "e2e": {"value": round(value, 3), "unit": "GB/s", "h2d_bytes_per_step": int(total), "d2h_bytes_per_step": int(d2h),
+                    "steps": ksteps, "ms_per_step": round(dt / ksteps * 1e3, 3), "h2d_peak": round(h2d_peak, 3),
+                    "frac": round(value / h2d_peak, 4),
+                    "h2d_peak_how": "one cudaMemcpyAsync per device of its share of the same pinned buffer, %d threads at once, "
+                                    "best of 2, wall clock" % ndev,
+                    "path": "xsg_search_host_multi: ONE pinned host buffer -> segments dealt round-robin to %d devices -> "
+                            "scans -> one result in file order -> D2H (wall clock of the host-synchronous calls)" % ndev},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": None, "parity": parity, "cpu_baseline": cpu,
+        }
+        xs.lib.xsg_host_free(hp)
+        mc.close()
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    if bad:
+        raise SystemExit("bench.py: %d result elements differ from the reference" % bad)
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.single_process and args.gpus > 1:
+        run_single_process(args)
     else:
         run_ours(args)
 

@@ -756,14 +756,33 @@ class Searcher {
     // read (two around a block edge)
     const size_t nlanes = _lanes.size();
     const size_t nbuf = nlanes + 3;
-    const auto t_alloc = std::chrono::steady_clock::now();
-    for (size_t i = 0; i < nbuf && i < _blocks.size() + 1 && !_blocks.empty(); ++i) {
-      auto b = std::make_unique<detail::Pinned>();
-      if (!b->alloc(static_cast<size_t>(_headroom + _max_block + 64))) throw std::runtime_error(detail::last_error("pinned buffer"));
-      _bufs.push_back(std::move(b));
-      _free.push_back(static_cast<int>(i));
-    }
-    _pinned_alloc_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_alloc).count();
+    // The buffers are page-locked one after the other on a thread of its own: the readers start on the first one
+    // while the others are still being pinned (page-locking costs as much per byte as reading from the page cache).
+    const size_t want = _blocks.empty() ? 0 : std::min(nbuf, _blocks.size() + 1);
+    _bufs.reserve(want);  // readers index _bufs without the lock: it must never reallocate
+    std::thread allocator([this, want] {
+      const auto t_alloc = std::chrono::steady_clock::now();
+      for (size_t i = 0; i < want && !_failed.load(); ++i) {
+        auto b = std::make_unique<detail::Pinned>();
+        if (!b->alloc(static_cast<size_t>(_headroom + _max_block + 64))) {
+          fail(detail::last_error("pinned buffer"));
+          break;
+        }
+        {
+          std::unique_lock lock(_m);
+          _bufs.push_back(std::move(b));
+          _free.push_back(static_cast<int>(i));
+        }
+        _cv.notify_all();
+      }
+      _pinned_alloc_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_alloc).count();
+    });
+    struct Joiner {  // whatever way this function is left: the allocator thread is collected first
+      std::thread& t;
+      ~Joiner() {
+        if (t.joinable()) t.join();
+      }
+    } join_allocator{allocator};
     _ready.assign(_blocks.size(), -1);
     _slices_left.assign(_blocks.size(), 0);
     for (int t = 0; t < _num_readers; ++t) _readers.emplace_back(&Searcher::run_reader, this);

@@ -19,7 +19,7 @@ ls -l $F > $O
 echo "host cores: $(nproc)" >> $O
 : > $O.err
 for tag in count lines; do
-  for r in 1 4 8 12; do
+  for r in 1 4 8 16; do
     for rep in 1 2; do
       s=$(date +%s.%N)
       n=$(./xsearch_b200/cpp/xsgrep --tag $tag --readers $r Sherlock $F 2>> $O.err | wc -l)
@@ -30,7 +30,7 @@ for tag in count lines; do
 done
 # reader mode A/B (xs::Options::reader_mode): memcpy out of a mapping instead of pread, DESIGN.md 8
 for mode in pread mmap; do
-  for r in 1 4 8 12; do
+  for r in 1 4 8 16; do
     ./xsearch_b200/cpp/xsgrep --tag count --readers $r --reader $mode Sherlock $F 2>> $O.err > /dev/null
     echo "tag=count reader=$mode readers=$r | $(tail -1 $O.err)" >> $O
   done

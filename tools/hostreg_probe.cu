@@ -118,8 +118,82 @@ int main(int argc, char** argv) {
     CK(cudaFreeHost(h));
   }
 
-  // B: register slices of the mapping
+  // E: what page-locking costs (the fixed cost of a one-shot file search)
+  for (size_t mb : {64, 256}) {
+    void* h = nullptr;
+    double t0 = now();
+    CK(cudaHostAlloc(&h, mb << 20, cudaHostAllocDefault));
+    const double t_alloc = now() - t0;
+    t0 = now();
+    CK(cudaFreeHost(h));
+    const double t_free = now() - t0;
+    // anonymous memory, huge pages advised, first touch by 8 threads, then registered
+    const size_t bytes = mb << 20;
+    t0 = now();
+    uint8_t* m = (uint8_t*)::aligned_alloc(2 << 20, bytes);
+    ::madvise(m, bytes, MADV_HUGEPAGE);
+    {
+      std::vector<std::thread> th;
+      for (int t = 0; t < 8; ++t) th.emplace_back([&, t] { std::memset(m + bytes / 8 * t, 0, bytes / 8); });
+      for (auto& x : th) x.join();
+    }
+    const double t_touch = now() - t0;
+    t0 = now();
+    CK(cudaHostRegister(m, bytes, cudaHostRegisterDefault));
+    const double t_reg = now() - t0;
+    t0 = now();
+    CK(cudaMemcpyAsync(dev, m, bytes < 2 * S ? bytes : 2 * S, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    const double t_cp = now() - t0;
+    t0 = now();
+    CK(cudaHostUnregister(m));
+    const double t_unreg = now() - t0;
+    ::free(m);
+    std::printf("E %3zu MiB: cudaHostAlloc %.1f ms, cudaFreeHost %.1f ms | THP alloc+touch(8 thr) %.1f ms, cudaHostRegister %.1f ms, H2D %.2f GB/s, unregister %.1f ms\n",
+                mb, t_alloc * 1e3, t_free * 1e3, t_touch * 1e3, t_reg * 1e3, (bytes < 2 * S ? bytes : 2 * S) / t_cp / 1e9, t_unreg * 1e3);
+  }
+
+  // B0: other ways to map the file before registering it
   {
+    int attr = -1;
+    cudaDeviceGetAttribute(&attr, cudaDevAttrHostRegisterReadOnlySupported, 0);
+    std::printf("B0 cudaDevAttrHostRegisterReadOnlySupported = %d\n", attr);
+    int attr2 = -1;
+    cudaDeviceGetAttribute(&attr2, cudaDevAttrPageableMemoryAccess, 0);
+    std::printf("B0 cudaDevAttrPageableMemoryAccess = %d\n", attr2);
+    struct V { const char* name; int oflag; int prot; int mflag; };
+    const V vs[] = {{"O_RDWR  PROT_RW MAP_SHARED ", O_RDWR, PROT_READ | PROT_WRITE, MAP_SHARED},
+                    {"O_RDONLY PROT_RW MAP_PRIVATE", O_RDONLY, PROT_READ | PROT_WRITE, MAP_PRIVATE},
+                    {"O_RDONLY PROT_R  MAP_PRIVATE", O_RDONLY, PROT_READ, MAP_PRIVATE}};
+    for (const V& v : vs) {
+      int fd = ::open(path, v.oflag);
+      uint8_t* m = (uint8_t*)::mmap(nullptr, N, v.prot, v.mflag, fd, 0);
+      if (m == MAP_FAILED) { std::printf("B0 %s: mmap failed\n", v.name); ::close(fd); continue; }
+      for (unsigned flag : {(unsigned)cudaHostRegisterDefault, (unsigned)cudaHostRegisterReadOnly}) {
+        double t0 = now();
+        cudaError_t e = cudaHostRegister(m, S, flag);
+        const double t_reg = now() - t0;
+        if (e != cudaSuccess) {
+          std::printf("B0 %s flag=%u: cudaHostRegister -> %s\n", v.name, flag, cudaGetErrorString(e));
+          cudaGetLastError();
+          continue;
+        }
+        t0 = now();
+        CK(cudaMemcpyAsync(dev, m, S, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        const double t_cp = now() - t0;
+        t0 = now();
+        CK(cudaHostUnregister(m));
+        std::printf("B0 %s flag=%u: register 256 MiB %.1f ms (%.2f GB/s), H2D %.2f GB/s, unregister %.1f ms\n", v.name, flag,
+                    t_reg * 1e3, S / t_reg / 1e9, S / t_cp / 1e9, (now() - t0) * 1e3);
+      }
+      ::munmap(m, N);
+      ::close(fd);
+    }
+  }
+
+  // B: register slices of the mapping
+  if (argc > 4) {
     int fd = ::open(path, O_RDONLY);
     for (int populate = 0; populate < 2; ++populate) {
       uint8_t* m = (uint8_t*)::mmap(nullptr, N, PROT_READ, MAP_SHARED | (populate ? MAP_POPULATE : 0), fd, 0);

@@ -173,8 +173,8 @@ def _check(rc: int) -> None:
         raise XsgError(rc, (lib.xsg_last_error() or b"").decode("utf-8", "replace"))
 
 
-from .api import (Context, MultiContext, Corpus, Result, Searcher, Stream, Exchange, extern_search, synth_host, chunk_bounds_host, pinned_empty,  # noqa: E402
+from .api import (Context, MultiContext, Corpus, Result, Searcher, Stream, Exchange, extern_search, synth_host, chunk_bounds_host, read_meta_bounds, pinned_empty,  # noqa: E402
                   shard_chunks, shard_exchange, sharded_scan, sharded_scan_async)
 
-__all__ = ["Context", "MultiContext", "Corpus", "Result", "Searcher", "Stream", "Exchange", "extern_search", "synth_host", "chunk_bounds_host", "pinned_empty",
+__all__ = ["Context", "MultiContext", "Corpus", "Result", "Searcher", "Stream", "Exchange", "extern_search", "synth_host", "chunk_bounds_host", "read_meta_bounds", "pinned_empty",
            "shard_chunks", "shard_exchange", "sharded_scan", "sharded_scan_async", "XsgError", "SynthParams", "ScanOpts", "Timings", "lib", "TAGS", "EXPORTS"]

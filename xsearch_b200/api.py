@@ -64,6 +64,30 @@ def pinned_empty(n: int, dtype=np.uint64) -> np.ndarray:
     return np.frombuffer(buf, dtype=dt, count=int(n))
 
 
+def read_meta_bounds(path: str) -> np.ndarray:
+    """Chunk table of an x-search v1 meta file as exclusive chunk ends (format: include/xsearch_b200/metafile.hpp;
+    u32 compression type, then per chunk 5 x u64 + n_map x (u64, u64)).  Compressed inputs are rejected like in the
+    C++ layer."""
+    import struct
+    raw = open(path, "rb").read()
+    if len(raw) < 4:
+        raise ValueError("meta file '%s' is truncated" % path)
+    (ctype,) = struct.unpack_from("<I", raw, 0)
+    if ctype != 1:
+        raise ValueError("compressed inputs (meta file compression type %d) are outside the GPU path" % ctype)
+    pos, ends, expect = 4, [], 0
+    while pos < len(raw):
+        if pos + 40 > len(raw):
+            raise ValueError("meta file '%s' is truncated" % path)
+        off, _, size, _, n_map = struct.unpack_from("<5Q", raw, pos)
+        pos += 40 + 16 * n_map
+        if pos > len(raw) or off != expect or size == 0:
+            raise ValueError("meta file '%s' is truncated or has a gap in its chunk table" % path)
+        expect = off + size
+        ends.append(expect)
+    return np.array(ends, dtype=np.uint64)
+
+
 def chunk_bounds_host(buf: np.ndarray, min_chunk: int = DEFAULT_MIN_CHUNK) -> np.ndarray:
     """v1 chunking rule (>= min_chunk bytes, extended through the next newline) on a host buffer."""
     n = int(buf.size)
@@ -421,15 +445,23 @@ class Searcher:
         self.kind, self.pattern, self.file_path = kind, pattern, file_path
         self._size, self._values, self._error = 0, [], None
         self._device, self._min_chunk, self._ignore_case = device, min_chunk, ignore_case
+        # num_threads / max_num_readers: accepted like the reference's; this Python mirror reads the file in one piece
+        # (the C++ layer, include/xsearch_b200/xsearch.hpp, is the one with reader threads and pinned segments)
+        self._meta_file = meta_file or None
         self._thread = threading.Thread(target=self._run, daemon=True)
         self._thread.start()
 
     def _run(self) -> None:
         try:
             data = np.fromfile(self.file_path, dtype=np.uint8)
+            bounds = None
+            if self._meta_file:  # the chunk table of a v1 meta file is the reference-chunk boundary list
+                bounds = read_meta_bounds(self._meta_file)
+                if (int(bounds[-1]) if bounds.size else 0) != data.size:
+                    raise ValueError("the meta file does not describe this file")
             ctx = Context(self._device)
             try:
-                res = ctx.search_host(data, None, self.pattern, self.kind, min_chunk=self._min_chunk,
+                res = ctx.search_host(data, None, self.pattern, self.kind, bounds=bounds, min_chunk=self._min_chunk,
                                       ignore_case=self._ignore_case)
                 self._size = res.count(self.kind)
                 if self.kind == LINES:

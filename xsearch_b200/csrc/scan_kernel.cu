@@ -203,41 +203,50 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
         f2 = keep_lanes(f2, lim - 8);
         f3 = keep_lanes(f3, lim - 12);
       }
-      const uint32_t c_row = __popc(f0) + __popc(f1) + __popc(f2) + __popc(f3);
-      r.cnt += c_row;
-      // OVL: an overlapping pair needs two occurrences within m - 1 <= 3 bytes: either both in this lane's 16
-      // bytes, or the first one in its last three bytes.  Rows where no lane qualifies (three out of four for
-      // a word like "that") skip the test altogether.
-      if (OVL && __any_sync(kFull, c_row >= 2 || (f3 & 0x80808000u) != 0)) {
-        // occurrence flags sit at bit 7 of their byte lane: the flag of position j + d, shifted down by d lanes,
-        // meets the flag of position j.  The word behind this lane's 16 bytes is word 0 of the next lane; for
-        // lane 31 that is another row or granule, so its last word is checked byte-wise instead.
-        uint32_t f4 = __shfl_sync(kFull, f0, (lane + 1) & 31);
-        if (lane == 31) f4 = 0;
-        // For m <= 4 every period is a multiple of the smallest one p, and occurrences at q and q + kp imply
-        // one at q + p: testing the distance p alone is enough (shift = 8p bits, a run-time uniform value).
-        const uint32_t sh = pat.ovl_shift;
-        r.ovl |= (f0 & __funnelshift_r(f0, f1, sh)) | (f1 & __funnelshift_r(f1, f2, sh)) |
-                 (f2 & __funnelshift_r(f2, f3, sh)) | (f3 & __funnelshift_r(f3, f4, sh));
-        if (lane == 31 && f3 != 0) {
-          for (int j = 4 - (NS - 1); j < 4; ++j) {
-            if (!((f3 >> (8 * j + 7)) & 1)) continue;
-            for (int d = 4 - j; d < NS; ++d) {
-              const long long q2 = (long long)(pos0 + 12 + j + d);
+      // The logic ops above saturate the ALU pipe, so everything that follows is written for the multiply-add pipe.
+      // A flag is 0x80 in its byte lane: dp4a with the weights (1, 2, 4, 8) / (16, 32, 64, 128) sums the flags of two
+      // words into 0x80 x (their eight flags as a byte) -- four IDP per row instead of shifts, multiplies and byte
+      // permutes on the ALU pipe -- and dp4a with the weights (1, 1, 1, 1) counts them (0x80 x count), no popc.
+      uint32_t row16 = 0;  // the 16 occurrence flags of this lane's 16 bytes, bit i <=> byte i
+      auto pack_row = [&]() {
+        const uint32_t lo = __dp4a(f1, 0x80402010u, __dp4a(f0, 0x08040201u, 0u));  // bits 7..14: words 0, 1
+        const uint32_t hi = __dp4a(f3, 0x80402010u, __dp4a(f2, 0x08040201u, 0u));  // bits 7..14: words 2, 3
+        row16 = add_on_fma_pipe(hi, 2u * k_one, lo >> 7);
+      };
+      if (EMIT) pack_row();
+      const uint32_t cnt_before = r.cnt;
+      if (!EMIT) {  // counted from the masks otherwise
+        r.cnt = __dp4a(f0, k_01, r.cnt);
+        r.cnt = __dp4a(f1, k_01, r.cnt);
+        r.cnt = __dp4a(f2, k_01, r.cnt);
+        r.cnt = __dp4a(f3, k_01, r.cnt);
+      }
+      // OVL: an overlapping pair needs two occurrences within m - 1 <= 3 bytes: either both in this lane's 16 bytes,
+      // or the first one in its last three bytes.  Rows where no lane qualifies (three out of four for a word like
+      // "that") skip the test altogether.
+      if (OVL && __any_sync(kFull, r.cnt - cnt_before >= 256u || (f3 & 0x80808000u) != 0)) {
+        // Two occurrences overlap iff they lie p < m bytes apart, p the smallest period (for m <= 4 every period is
+        // a multiple of the smallest one, and occurrences at q and q + kp imply one at q + p).  With the flags of
+        // this lane's 16 bytes in the low half of a word and those of the next lane's in the high half, that is one
+        // shift and one AND.  The bytes behind lane 31 belong to another row or granule: checked byte-wise.
+        pack_row();
+        uint32_t nxt = __shfl_sync(kFull, row16, (lane + 1) & 31);
+        if (lane == 31) nxt = 0;
+        const uint32_t m32 = add_on_fma_pipe(nxt, 65536u * k_one, row16);
+        r.ovl |= m32 & (m32 >> (pat.ovl_shift >> 3)) & 0xffffu;
+        if (lane == 31 && (row16 >> (16 - (NS - 1))) != 0) {
+          for (int j = 16 - (NS - 1); j < 16; ++j) {
+            if (!((row16 >> j) & 1)) continue;
+            for (int d = 16 - j; d < NS; ++d) {
+              const long long q2 = (long long)(pos0 + j + d);
               if (((pat.periods >> d) & 1) && q2 <= last_q && verify_at(buf, (uint64_t)q2, pat)) r.ovl |= 1;
             }
           }
         }
       }
-      if (EMIT && (f0 | f1 | f2 | f3)) {
-        // 16 flags (bit 7 of every byte lane of four words) -> 16 mask bits.  The flags of two words share one
-        // multiply: with word 0 moved down to bit 3 of its lanes, t * 0x00204081 collects all eight flags in
-        // the top byte (no two partial products meet: the flag positions are all 3 mod 4, the four shifts
-        // 0, 7, 14, 21 are distinct mod 4).  Byte permutes put the two bytes into this row's half of the
-        // mask register.  (Eight operations per row; four nibble gathers + shifts + ORs were thirteen.)
-        const uint32_t lo = ((f0 >> 4) | f1) * 0x00204081u, hi = ((f2 >> 4) | f3) * 0x00204081u;
-        const uint32_t row = __byte_perm(lo, hi, 0x0073);  // byte 0 = lo.b3, byte 1 = hi.b3 (bytes 2, 3 unused)
-        r.mask[u >> 1] = __byte_perm(r.mask[u >> 1], row, (u & 1) ? 0x5410 : 0x3254);
+      if (EMIT) {  // two rows per mask register: even rows in the low half
+        if (u & 1) r.mask[u >> 1] = add_on_fma_pipe(row16, 65536u * k_one, r.mask[u >> 1]);
+        else r.mask[u >> 1] = row16;
       }
     } else {
       // filter: pattern byte a at this position AND pattern byte a+4 one word further
@@ -275,6 +284,10 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
         }
       }
     }
+  }
+  if (NS <= 4) {
+    if (EMIT) r.cnt = __popc(r.mask[0]) + __popc(r.mask[1]) + __popc(r.mask[2]) + __popc(r.mask[3]);
+    else r.cnt >>= 7;  // accumulated as 0x80 x count
   }
 }
 
@@ -369,34 +382,157 @@ __device__ __forceinline__ void sts16_if(uint32_t addr, uint32_t val, uint32_t c
       "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p st.shared.u16 [%0+%3], %1;\n\t}"
       :: "r"(addr), "h"((unsigned short)val), "r"(cond), "n"(OFF) : "memory");
 }
-// positions (base + bit index) of the three lowest set bits of w -> stage entries 0..2 at shared address saddr;
-// returns the bits that are left
-__device__ __forceinline__ uint32_t stage_three(uint32_t w, uint32_t saddr, uint32_t base) {
-  sts16_if<0>(saddr, base + __ffs(w) - 1, w);
-  w &= w - 1;
-  sts16_if<2>(saddr, base + __ffs(w) - 1, w);
-  w &= w - 1;
-  sts16_if<4>(saddr, base + __ffs(w) - 1, w);
-  return w & (w - 1);
-}
-__device__ __forceinline__ void stage_rest(uint32_t w, uint32_t saddr, uint32_t base) {
-  saddr += 6;
-#pragma unroll 1
-  while (w) {
-    sts16_if<0>(saddr, base + __ffs(w) - 1, 1u);
-    w &= w - 1;
-    saddr += 2;
-  }
+// st.shared.v2.u32 [addr], {x, y}  -- executed only if cond != 0
+__device__ __forceinline__ void sts64_if(uint32_t addr, uint32_t x, uint32_t y, uint32_t cond) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.shared.v2.u32 [%0], {%1, %2};\n\t}"
+      :: "r"(addr), "r"(x), "r"(y), "r"(cond) : "memory");
 }
 
 constexpr uint32_t kStageCap = 1024;   // hits staged per warp (2 KiB); denser granules (>= 1 hit per 4 bytes) go direct
 constexpr uint32_t kStageMin = 16;     // below this many hits staging costs more than it saves
+constexpr uint32_t kQueueCap = 128;    // mask words of one granule
 
-__global__ void __launch_bounds__(kThreads, 8)
+// Expansion of one hit granule, dense case.  A lane holds the 128 mask bits of 128 consecutive corpus bytes: on
+// English text a 32-bit word of them holds 0.6 hits, so walking "the k-th hit of my j-th word" in lock step leaves
+// four lanes out of five idle in every step (round 1: twelve predicated chains per lane, 3.3 warp instructions per
+// emitted offset).  Instead the NON-EMPTY words are queued in shared memory first -- every lane appends its own at the
+// warp-scanned position, each entry carrying its first output slot -- and the lanes then take one queued word each:
+// every lane of a round has at least one hit to place, and a second one in a quarter of the cases.
+__device__ __forceinline__ void expand_queued(const GranMask& cur, uint32_t hits_excl, uint32_t nz_excl, uint32_t qn,
+                                              int lane, uint2* __restrict__ queue, uint16_t* __restrict__ stage) {
+  const uint32_t qaddr = (uint32_t)__cvta_generic_to_shared(queue);
+  const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(stage);
+  uint32_t q = qaddr + 8 * nz_excl;
+  uint32_t tag = (hits_excl << 16) | (uint32_t)(lane * 128);  // {first output slot, position of bit 0} of word 0
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t w = cur.w[k];
+    sts64_if(q, w, tag, w);
+    q += w ? 8u : 0u;
+    tag += ((uint32_t)__popc(w) << 16) + 32u;
+  }
+  __syncwarp();
+#pragma unroll 1
+  for (uint32_t e = lane; e < qn; e += 32) {
+    const uint2 it = queue[e];
+    uint32_t w = it.x;
+    const uint32_t base = it.y & 0xffffu;
+    const uint32_t dst = saddr + 2 * (it.y >> 16);
+    sts16_if<0>(dst, base + __ffs(w) - 1, 1u);  // a queued word is not empty
+    w &= w - 1;
+    sts16_if<2>(dst, base + __ffs(w) - 1, w);
+    w &= w - 1;
+    uint32_t d = dst + 4;
+#pragma unroll 1
+    while (w) {  // three and more hits in four bytes of text: rare
+      sts16_if<0>(d, base + __ffs(w) - 1, 1u);
+      w &= w - 1;
+      d += 2;
+    }
+  }
+  __syncwarp();
+}
+
+// A unit whose 32 granules ALL hold two or more occurrences (a frequent short pattern): no search for the next hit
+// granule, no per-granule base from a shuffle -- the output of the unit is one contiguous run, so the base just
+// advances by every granule's total -- and 32-bit shared-memory addresses and pointer increments throughout: this
+// kernel is bound by instruction issue (ncu: 93 % of the issue slots), every instruction per granule is time.
+__device__ __forceinline__ void emit_dense_unit(const Pattern& pat, const ScanArgs& a, uint64_t g0, int lane,
+                                                uint2* __restrict__ queue, uint16_t* __restrict__ stage) {
+  const uint32_t qaddr = (uint32_t)__cvta_generic_to_shared(queue);
+  const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(stage);
+  const uint4* __restrict__ mp = a.gran_mask + g0 * 32 + lane;
+  unsigned long long base = a.gran_prefix[g0];
+  uint64_t pos0 = g0 * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add;
+  uint64_t* __restrict__ outp = a.occ + base + lane;  // this lane's first output slot of the current granule
+  uint4 nxt = __ldg(mp);
+#pragma unroll 1
+  for (int i = 0; i < 32; ++i) {
+    const uint4 cur = nxt;
+    mp += 32;
+    if (i < 31) nxt = __ldg(mp);
+    const uint32_t c0 = __popc(cur.x), c1 = __popc(cur.y), c2 = __popc(cur.z), c3 = __popc(cur.w);
+    const uint32_t n0 = min(c0, 1u), n1 = min(c1, 1u), n2 = min(c2, 1u), n3 = min(c3, 1u);
+    // one warp scan for both: hits (low half) and non-empty words (high half) before this lane
+    const uint32_t mine = (c0 + c1 + c2 + c3) + ((n0 + n1 + n2 + n3) << 16);
+    const uint32_t inc = warp_inclusive_scan(mine);
+    const uint32_t all = __shfl_sync(kFull, inc, 31);
+    const uint32_t total = all & 0xffffu, qn = all >> 16;
+    const uint32_t excl = inc - mine;
+    if (base + total <= a.occ_cap) {  // (only an estimate-sized list of the non-direct path can be too short)
+      if (total <= kStageCap) {
+        // queue the non-empty words: {mask word, first output slot x 2 (a byte offset into the stage) : position of bit 0}
+        uint32_t q = qaddr + 8 * (excl >> 16);
+        uint32_t tag = ((excl & 0xffffu) << 17) | (uint32_t)(lane * 128);
+        sts64_if(q, cur.x, tag, cur.x);
+        q += 8 * n0;
+        tag += (c0 << 17) + 32u;
+        sts64_if(q, cur.y, tag, cur.y);
+        q += 8 * n1;
+        tag += (c1 << 17) + 32u;
+        sts64_if(q, cur.z, tag, cur.z);
+        q += 8 * n2;
+        tag += (c2 << 17) + 32u;
+        sts64_if(q, cur.w, tag, cur.w);
+        __syncwarp();
+#pragma unroll 1
+        for (uint32_t e = lane; e < qn; e += 32) {  // one queued word per lane: at least one hit to place
+          uint32_t w, t;
+          asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w), "=r"(t) : "r"(qaddr + 8 * e));
+          const uint32_t bpos = t & 0xffffu;
+          const uint32_t dst = saddr + (t >> 16);
+          sts16_if<0>(dst, bpos + __ffs(w) - 1, 1u);
+          w &= w - 1;
+          sts16_if<2>(dst, bpos + __ffs(w) - 1, w);
+          w &= w - 1;
+          uint32_t d = dst + 4;
+#pragma unroll 1
+          while (w) {  // three and more hits in four bytes of text: rare
+            sts16_if<0>(d, bpos + __ffs(w) - 1, 1u);
+            w &= w - 1;
+            d += 2;
+          }
+        }
+        __syncwarp();
+        // coalesced write-out: 32 consecutive offsets per store instruction
+        uint64_t* __restrict__ o = outp;
+#pragma unroll 1
+        for (uint32_t j = lane; j < total; j += 32) {
+          uint32_t v;
+          asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(saddr + 2 * j));
+          *o = pos0 + v;
+          o += 32;
+        }
+        __syncwarp();  // stage and queue are rewritten for the next granule
+      } else {  // denser than one hit per four bytes: every lane stores its own positions
+        uint64_t* __restrict__ o = outp - lane + (excl & 0xffffu);
+        const uint64_t p = pos0 + (uint32_t)(lane * 128);
+        const uint32_t ws[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint32_t w = ws[k];
+#pragma unroll 1
+          while (w) {
+            const int b = __ffs(w) - 1;
+            w &= w - 1;
+            *o++ = p + (uint32_t)(32 * k + b);
+          }
+        }
+      }
+    }
+    base += total;
+    outp += total;
+    pos0 += kGranuleBytes;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 6)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   pdl_wait();
   pdl_trigger();
   __shared__ uint16_t s_stage[kWarps][kStageCap];
+  __shared__ uint2 s_queue[kWarps][kQueueCap];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const uint64_t n_gran = a.n_tiles * kWarps;
@@ -411,6 +547,10 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   }
   unsigned todo = __ballot_sync(kFull, c > 1);
   if (todo == 0) return;
+  if (todo == kFull) {  // every granule of the unit holds several occurrences: the dense case, as a straight loop
+    emit_dense_unit(pat, a, g0, lane, s_queue[warp], s_stage[warp]);
+    return;
+  }
   // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below).  The
   // masks are expanded one granule after the other with the next one in flight; to make that next load an L2
   // hit rather than a DRAM access, the masks of the hit granules four ahead are pulled into L2 (only four:
@@ -441,22 +581,21 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
       if (t != 0 && lane < 4)
         asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(a.gran_mask + (g0 + (__ffs(t) - 1)) * 32) + 128 * lane));
     }
+    // one warp scan for both: hits (low half) and non-empty words (high half) before this lane
     const uint32_t cnt = __popc(cur.w[0]) + __popc(cur.w[1]) + __popc(cur.w[2]) + __popc(cur.w[3]);
-    uint32_t inc = cnt;  // inclusive warp scan of the per-lane counts
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(kFull, inc, o);
-      if (lane >= o) inc += t;
-    }
-    const uint32_t total = __shfl_sync(kFull, inc, 31);
+    const uint32_t nzc = (cur.w[0] != 0) + (cur.w[1] != 0) + (cur.w[2] != 0) + (cur.w[3] != 0);
+    const uint32_t mine = cnt | (nzc << 16);
+    const uint32_t inc = warp_inclusive_scan(mine);
+    const uint32_t all = __shfl_sync(kFull, inc, 31);
+    const uint32_t total = all & 0xffffu;
     // one capacity check per granule (the list is sized from the exact total; it only overflows on the
     // estimate-based first attempt of the non-direct path)
     if (base + total > a.occ_cap) continue;
-    uint32_t slot = inc - cnt;
+    const uint32_t excl = inc - mine;
     uint64_t* __restrict__ out = a.occ + base;
     const uint64_t pos0 = (g0 + src) * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add;
     if (total < kStageMin || total > kStageCap) {
-      uint64_t* __restrict__ o = out + slot;
+      uint64_t* __restrict__ o = out + (excl & 0xffffu);
       const uint64_t p = pos0 + (uint32_t)(lane * 128);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -469,28 +608,10 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
         }
       }
     } else {
-      // a word of a dense text search holds one hit, sometimes two or three: the first three hits of all four
-      // words are taken by straight-line predicated code (twelve independent chains, no branch), the rare
-      // rest by a loop
-      const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(stage) + 2 * slot;
-      const uint32_t s1 = s0 + 2 * __popc(cur.w[0]);
-      const uint32_t s2 = s1 + 2 * __popc(cur.w[1]);
-      const uint32_t s3 = s2 + 2 * __popc(cur.w[2]);
-      const uint32_t pb = (uint32_t)(lane * 128);
-      const uint32_t r0 = stage_three(cur.w[0], s0, pb);
-      const uint32_t r1 = stage_three(cur.w[1], s1, pb + 32);
-      const uint32_t r2 = stage_three(cur.w[2], s2, pb + 64);
-      const uint32_t r3 = stage_three(cur.w[3], s3, pb + 96);
-      if (__any_sync(kFull, (r0 | r1 | r2 | r3) != 0)) {
-        stage_rest(r0, s0, pb);
-        stage_rest(r1, s1, pb + 32);
-        stage_rest(r2, s2, pb + 64);
-        stage_rest(r3, s3, pb + 96);
-      }
-      __syncwarp();
+      expand_queued(cur, excl & 0xffffu, excl >> 16, all >> 16, lane, s_queue[warp], stage);
 #pragma unroll 1
       for (uint32_t j = lane; j < total; j += 32) out[j] = pos0 + stage[j];
-      __syncwarp();  // the stage is rewritten for the next hit granule
+      __syncwarp();  // stage and queue are rewritten for the next hit granule
     }
   }
 }

@@ -202,6 +202,16 @@ constexpr unsigned long long kValueMask = (1ull << kStatusShift) - 1;
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(kFull, v); }
 
+// inclusive warp scan, two instructions per step: the shuffle itself says (predicate) whether a lane had a source
+__device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+    asm volatile(
+        "{\n\t.reg .u32 t;\n\t.reg .pred p;\n\tshfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t@p add.u32 %0, %0, t;\n\t}"
+        : "+r"(v) : "r"(o));
+  return v;
+}
+
 
 // Decoupled look-back (Merrill & Garland): returns the exclusive prefix of `aggregate` over all
 // tiles before `tile`; called by warp 0 only.  Tiles are handed out by a ticket counter, so every
