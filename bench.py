@@ -430,7 +430,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def reduce_ranks(v, op):
-        if world == 1:
+        if world == 1 or op is None:
             return v
         t = torch.tensor([v], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=op)
@@ -543,11 +543,20 @@ def run_ours(args):
     e2e = None
     streamed = None  # outputs of the last host-streamed search
     hp = None
-    if not args.no_e2e or not args.no_cpu:
+    # does this rank's share of the host RAM hold its whole shard (plus result vectors)?  If not -- 8 x 50 GB on a box
+    # with less than 400 GB -- there is no host-streamed leg, and the parity block checks a prefix and the last chunks
+    # of the shard instead of all of it (fresh GPU scans of exactly those byte ranges)
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    host_budget = int(0.7 * host_mem_available() / max(1, local_world))
+    if os.environ.get("XSG_BENCH_HOST_BUDGET_GB"):  # to exercise the prefix/tail parity path on a box with plenty of RAM
+        host_budget = int(float(os.environ["XSG_BENCH_HOST_BUDGET_GB"]) * GB)
+    fits = reduce_ranks(1.0 if nbytes + (64 << 20) <= host_budget else 0.0, dist.ReduceOp.MIN if world > 1 else None) > 0.5
+    no_e2e = args.no_e2e or not fits
+    if (not no_e2e or not args.no_cpu) and fits:
         hp = C.c_void_p()
         xs._check(xs.lib.xsg_host_alloc(nbytes, C.byref(hp)))
         xs._check(xs.lib.xsg_corpus_download(corpus._h, hp, 0, nbytes))  # same bytes, now in pinned host RAM
-    if not args.no_e2e:
+    if not no_e2e:
         ksteps = args.e2e_steps or min(args.steps, 6)
         d2h = 0
         pinned_out = {}
@@ -632,37 +641,71 @@ def run_ours(args):
             cap = max(1 << 20, gpu_count + gpu_count // 8 + 1024)
             best, exp = None, None
             passes = max(1, args.cpu_passes) if world == 1 else 1
-            for _ in range(passes):
-                t0 = time.perf_counter()
-                exp = chk.run_tags(tags, hp.value, nbytes, pat, bounds, nthreads, cap)
-                dt = time.perf_counter() - t0
-                best = dt if best is None or dt < best else best
-            # line-index base of this shard from an independent newline count of every shard (host cores), gathered
-            # outside the timed region
-            line_base = 0
-            if world > 1:
-                my_nl = int(corpus_lib().xsc_count_newlines(hp.value, nbytes, nthreads))
-                t = torch.tensor([my_nl], dtype=torch.int64, device="cuda")
-                allnl = [torch.empty_like(t) for _ in range(world)]
-                dist.all_gather(allnl, t)
-                line_base = int(sum(int(x.item()) for x in allnl[:rank]))
             bad = checked = 0
             legs = []
-            for name, got in (("device-resident", resident), ("host-streamed", streamed)):
-                if got is None:
-                    continue
-                b, c = compare_outputs(tags, got, exp, shard_base, line_base)
-                bad += b
-                checked += c
-                legs.append(name)
+            checked_bytes = 0
+            if fits:
+                for _ in range(passes):
+                    t0 = time.perf_counter()
+                    exp = chk.run_tags(tags, hp.value, nbytes, pat, bounds, nthreads, cap)
+                    dt = time.perf_counter() - t0
+                    best = dt if best is None or dt < best else best
+                # line-index base of this shard from an independent newline count of every shard (host cores),
+                # gathered outside the timed region
+                line_base = 0
+                if world > 1:
+                    my_nl = int(corpus_lib().xsc_count_newlines(hp.value, nbytes, nthreads))
+                    t = torch.tensor([my_nl], dtype=torch.int64, device="cuda")
+                    allnl = [torch.empty_like(t) for _ in range(world)]
+                    dist.all_gather(allnl, t)
+                    line_base = int(sum(int(x.item()) for x in allnl[:rank]))
+                for name, got in (("device-resident", resident), ("host-streamed", streamed)):
+                    if got is None:
+                        continue
+                    b, c = compare_outputs(tags, got, exp, shard_base, line_base)
+                    bad += b
+                    checked += c
+                    legs.append(name)
+                checked_bytes = nbytes
+            else:
+                # prefix and tail of the shard, whole reference chunks, as much as the host budget allows: each range
+                # is brought to the host, scanned by the reference there and by a fresh GPU scan of the same bytes
+                nb = int(bounds.size)
+                half = max(1, host_budget // 3)
+                j = int(np.searchsorted(bounds, half, side="right"))          # chunks [0, j) fit
+                k = int(np.searchsorted(bounds, int(bounds[-1]) - half, side="left")) + 1  # chunks [k, nb) fit
+                ranges = [(0, max(1, j))] + ([(max(k, j), nb)] if max(k, j) < nb else [])
+                for lo, hi in ranges:
+                    b0 = int(bounds[lo - 1]) if lo else 0
+                    b1 = int(bounds[hi - 1])
+                    hb = xs.pinned_empty(b1 - b0, dtype=np.uint8)
+                    xs._check(xs.lib.xsg_corpus_download(corpus._h, C.c_void_p(hb.ctypes.data), b0, b1 - b0))
+                    rel = (bounds[lo:hi] - np.uint64(b0)).astype(np.uint64)
+                    t0 = time.perf_counter()
+                    e = chk.run_tags(tags, hb.ctypes.data, b1 - b0, pat, rel, nthreads, cap)
+                    dt = time.perf_counter() - t0
+                    best = (best or 0.0) + dt
+                    with torch.cuda.stream(stream):
+                        sub = ctx.corpus_from_host(hb, bounds=rel)
+                        r = ctx.scan(sub, pat, kinds, offset_base=shard_base + b0)
+                        got = gpu_outputs(r)
+                        r.free()
+                        sub.free()
+                    b, c = compare_outputs(tags, got, e, shard_base + b0, 0)
+                    bad += b
+                    checked += c
+                    checked_bytes += b1 - b0
+                    del hb
+                legs.append("device-resident, chunk ranges %s of %d chunks (host RAM holds no more)" % (ranges, nb))
             bad_all = int(sum_over_ranks(bad))
-            parity = {"oracle": chk.kind, "checked_bytes": int(nbytes), "checked_bytes_total": int(total_bytes),
+            parity = {"oracle": chk.kind, "checked_bytes": int(checked_bytes),
+                      "checked_bytes_total": int(sum_over_ranks(checked_bytes)),
                       "tags": list(tags), "legs": legs, "elements_compared": int(sum_over_ranks(checked)),
                       "mismatches": bad_all, "ranks": world,
                       "how": "every rank: the reference's wrappers over all bytes of its shard (same v1 chunks), vectors "
                              "compared element by element with the GPU's (shard byte base added; line indices + the "
                              "newline count of the lower shards, counted independently on the host)"}
-            if world == 1:
+            if world == 1 and fits:
                 cpu = {"value": round(nbytes / best / 1e9, 3), "unit": "GB/s", "cores": nthreads, "kind": chk.kind,
                        "sample": "all %.2f GB of the same corpus (pinned host RAM), v1 chunks, all requested tags per pass, "
                                  "best of %d passes; its vectors are the parity block's reference; xs::line_indices is "
