@@ -169,6 +169,10 @@ __global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_const
 #pragma unroll
     for (int i = 0; i < kExItems; ++i) x[i] = base + i < n ? in[base + i] : 0;
   }
+  if (blockIdx.y == 1) {  // the newline table: two 16-bit counts per granule (halves), scanned as their sum
+#pragma unroll
+    for (int i = 0; i < kExItems; ++i) x[i] = (x[i] & 0xffffu) + (x[i] >> 16);
+  }
 #pragma unroll
   for (int i = 0; i < kExItems; ++i) v += x[i];
   uint32_t total;
@@ -282,12 +286,9 @@ void launch_add_u64(uint64_t* v, uint64_t n, uint64_t delta, cudaStream_t s) {
 
 void launch_synth(uint8_t* dst, uint64_t first_block, uint64_t n_blocks, const xsg_synth_params& p, cudaStream_t s) {
   if (n_blocks == 0) return;
-  static bool attr_set = false;
+  // (the attribute belongs to the function ON THE CURRENT DEVICE: a process that drives several devices sets it on each)
   const int smem = kSynthThreads * XSG_SYNTH_BLOCK;
-  if (!attr_set) {
-    cudaFuncSetAttribute(synth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    attr_set = true;
-  }
+  cudaFuncSetAttribute(synth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   // grid.x is limited to 2^31-1 CTAs of 32 blocks (128 KiB) each: far beyond 180 GB
   synth_kernel<<<(unsigned)div_up(n_blocks, kSynthThreads), kSynthThreads, smem, s>>>(dst, first_block, n_blocks, p);
 }

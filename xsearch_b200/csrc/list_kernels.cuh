@@ -23,7 +23,8 @@ void launch_check_bounds(const uint8_t* buf, uint64_t n, const uint64_t* bounds,
 // sum of a u32 array into *out (out must be zero before)
 void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, cudaStream_t s);
 // exclusive scans u32 -> u64 of one or two tables of n entries in ONE launch (out[i] = sum in[0..i),
-// out[n] = *total = sum); in_b may be nullptr.  desc holds 2 * div_up(n, 2048) look-back descriptors (tagged
+// out[n] = *total = sum); in_b may be nullptr.  Table B holds two 16-bit counts per entry (ScanArgs::nl_granule): their sum
+// is what is scanned.  desc holds 2 * div_up(n, 2048) look-back descriptors (tagged
 // with `epoch`, see lookback()), tickets two zeroed counters.  The tables must be 16-byte aligned.
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
                         uint64_t* out_b, unsigned long long* total_b, uint64_t n, unsigned long long* desc,
@@ -47,6 +48,7 @@ struct CompactArgs {
   uint64_t goff;               // global offset base
   uint64_t lidx_base;          // line index base
   const uint64_t* nl_prefix;   // [granules] exclusive '\n' prefix (line indices) or nullptr
+  const uint32_t* nl_halves;   // [granules] '\n' per half granule, 2 x u16 packed (ScanArgs::nl_granule)
   uint64_t* out_match;         // any of these may be nullptr
   uint64_t* out_line_off;
   uint64_t* out_line_idx;

@@ -57,7 +57,7 @@ __device__ __forceinline__ uint32_t not_newline_x128(uint32_t w, uint32_t acc, u
 struct LaneResult {
   uint32_t mask[kRows / 2];  // EMIT: 16 occurrence bits per row, two rows per register
   uint32_t cnt;              // occurrences owned by this lane
-  uint32_t nonnl;            // 128 x bytes that are not '\n' (zero padding included)
+  uint32_t nonnlh[2];        // per half of the granule (four rows): 128 x bytes that are not '\n' (padding included)
   uint32_t ovl;              // OVL: non-zero when an occurrence of this lane overlaps a later one
 };
 
@@ -139,10 +139,10 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
   const bool partial = gran_off + kGranuleBytes + 16 > n;
 
   r.cnt = 0;
-  r.nonnl = 0;
   r.ovl = 0;
 #pragma unroll
   for (int i = 0; i < kRows / 2; ++i) r.mask[i] = 0;
+  r.nonnlh[0] = r.nonnlh[1] = 0;
   const long long last_q = (long long)n - (long long)pat.m;  // last valid occurrence start
   // The filter variants take their constants from global memory so that they stay in
   // registers (ScanArgs::konst: saves nine constant-bank reads per row); the exact-compare variants are bound by
@@ -170,10 +170,11 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
     if (NL) {  // 128 x (bytes that are not '\n'), accumulated on the multiply-add pipe
-      r.nonnl = not_newline_x128(w0, r.nonnl, k_nl, k_7f, k_one, k_01);
-      r.nonnl = not_newline_x128(w1, r.nonnl, k_nl, k_7f, k_one, k_01);
-      r.nonnl = not_newline_x128(w2, r.nonnl, k_nl, k_7f, k_one, k_01);
-      r.nonnl = not_newline_x128(w3, r.nonnl, k_nl, k_7f, k_one, k_01);
+      uint32_t& acc = r.nonnlh[u >> 2];
+      acc = not_newline_x128(w0, acc, k_nl, k_7f, k_one, k_01);
+      acc = not_newline_x128(w1, acc, k_nl, k_7f, k_one, k_01);
+      acc = not_newline_x128(w2, acc, k_nl, k_7f, k_one, k_01);
+      acc = not_newline_x128(w3, acc, k_nl, k_7f, k_one, k_01);
     }
 
     uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
@@ -313,8 +314,11 @@ __device__ __forceinline__ bool count_tile(const Pattern& pat, const ScanArgs& a
   classify_granule<NS, MASK, NL, ICASE, OVL>(pat, a.buf, a.n, gran_off, lane, v, ext, a.konst, r);
   if (OVL && r.ovl != 0) *a.overlap = 1u;
   if (NL) {
-    const uint32_t s = warp_sum(r.nonnl) >> 7;
-    if (lane == 0) a.nl_granule[g] = kGranuleBytes - s;
+    // '\n' per half of the granule, both counts in ONE warp reduction (a lane holds 64 bytes of each half)
+    constexpr uint32_t kLaneHalf = kGranuleBytes / 2 / 32;
+    const uint32_t mine = (kLaneHalf - (r.nonnlh[0] >> 7)) | ((kLaneHalf - (r.nonnlh[1] >> 7)) << 16);
+    const uint32_t both = warp_sum(mine);
+    if (lane == 0) a.nl_granule[g] = both;
   }
   const uint32_t wcnt = warp_sum(r.cnt);
   if (lane == 0) a.gran_count[g] = wcnt;

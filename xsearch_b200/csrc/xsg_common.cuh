@@ -52,7 +52,9 @@ struct ScanArgs {
   uint64_t n;                // corpus size in bytes
   uint64_t n_tiles;          // CTAs of pass 1; n_tiles * kWarps granules
   uint32_t* gran_count;      // [granules] occurrences owned by each 4 KiB granule (ownership by anchor byte)
-  uint32_t* nl_granule;      // [granules] '\n' per granule (newline mode) or nullptr
+  uint32_t* nl_granule;      // [granules] '\n' per granule (newline mode) or nullptr, as TWO 16-bit counts: low half =
+                             // first 2 KiB of the granule, high half = second 2 KiB (the line-index stage rescans at
+                             // most 1 KiB; one packed warp reduction yields both)
   uint4* gran_mask;          // [granules x 32] occurrence bitmask (16 bits per lane and row) of every granule
                              // that holds two or more occurrences
   uint16_t* gran_first;      // [granules] position in the granule of the occurrence of a granule that holds ONE

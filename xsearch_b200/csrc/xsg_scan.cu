@@ -252,6 +252,11 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     // one set of launches scans both tables: granule occurrence counts and granule newline counts
     uint32_t epoch;
     if ((rc = next_epoch(ctx, &epoch))) return rc;
+    // direct mode: for xs::match_byte_offsets the occurrence list IS the result unless a chunk tail of the
+    // reference drops one (rare) or -- bordered patterns only -- two occurrences overlap somewhere (checked on
+    // the list).  So pass 2 writes global offsets straight into the result vector and the list kernels read
+    // it with a bias; the select + compact fall-back below covers the exceptions.
+    const bool direct = (kinds & XSG_MATCH_BYTE_OFFSETS) != 0;
     launch_exscan2_u32(a.gran_count, ctx->gran_prefix.as<uint64_t>(), &ds->occ_total, a.nl_granule,
                        want_idx ? ctx->nl_prefix.as<uint64_t>() : nullptr, &ds->nl_total, n_gran, scan_desc,
                        &ds->ticket[0], epoch, s);
@@ -262,11 +267,6 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
                              cudaMemcpyDeviceToHost, s));
     XSG_CUDA(cudaEventRecord(ctx->ev[4], s));
-    // direct mode: for xs::match_byte_offsets the occurrence list IS the result unless a chunk tail of the
-    // reference drops one (rare) or -- bordered patterns only -- two occurrences overlap somewhere (checked on
-    // the list).  So pass 2 writes global offsets straight into the result vector and the list kernels read
-    // it with a bias; the select + compact fall-back below covers the exceptions.
-    const bool direct = (kinds & XSG_MATCH_BYTE_OFFSETS) != 0;
     uint64_t k = 0;
     uint64_t* occ_list = nullptr;
     if (direct) {
@@ -329,6 +329,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         c.goff = goff;
         c.lidx_base = lidx_base;
         c.nl_prefix = ctx->nl_prefix.as<uint64_t>();
+        c.nl_halves = ctx->nl_granule.as<uint32_t>();
         if (fam == 0) {
           if (kinds & XSG_MATCH_BYTE_OFFSETS) {
             if ((rc = alloc_out(ctx, &part->match_off, k))) return rc;
