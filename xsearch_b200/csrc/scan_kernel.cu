@@ -440,8 +440,40 @@ __device__ __forceinline__ void expand_queued(const GranMask& cur, uint32_t hits
 
 // A unit whose 32 granules ALL hold two or more occurrences (a frequent short pattern): no search for the next hit
 // granule, no per-granule base from a shuffle -- the output of the unit is one contiguous run, so the base just
-// advances by every granule's total -- and 32-bit shared-memory addresses and pointer increments throughout: this
-// kernel is bound by instruction issue (ncu: 93 % of the issue slots), every instruction per granule is time.
+// advances by every round's total -- and 32-bit shared-memory addresses and pointer increments throughout: this
+// kernel is bound by instruction issue (ncu: 91 % of the issue slots), every instruction per granule is time.
+// The granules are taken TWO per round: one packed scan serves both (hits of A in the low half, of B in the high
+// half; the same for the non-empty words), and the fixed cost of a round -- loop control, capacity check, the warp
+// barriers around queue and stage, pointer updates -- is paid once per 8 KiB of text instead of once per 4 KiB.
+__device__ __forceinline__ void enqueue_words(const uint4& m, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t n0, uint32_t n1,
+                                              uint32_t n2, uint32_t q, uint32_t tag) {
+  // {mask word, first output slot x 2 (a byte offset into the stage) : position of bit 0}, non-empty words only
+  sts64_if(q, m.x, tag, m.x);
+  q += 8 * n0;
+  tag += (c0 << 17) + 32u;
+  sts64_if(q, m.y, tag, m.y);
+  q += 8 * n1;
+  tag += (c1 << 17) + 32u;
+  sts64_if(q, m.z, tag, m.z);
+  q += 8 * n2;
+  tag += (c2 << 17) + 32u;
+  sts64_if(q, m.w, tag, m.w);
+}
+
+__device__ __forceinline__ void store_own_positions(const uint4& m, uint64_t* __restrict__ o, uint64_t p) {
+  const uint32_t ws[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    uint32_t w = ws[k];
+#pragma unroll 1
+    while (w) {
+      const int b = __ffs(w) - 1;
+      w &= w - 1;
+      *o++ = p + (uint32_t)(32 * k + b);
+    }
+  }
+}
+
 __device__ __forceinline__ void emit_dense_unit(const Pattern& pat, const ScanArgs& a, uint64_t g0, int lane,
                                                 uint2* __restrict__ queue, uint16_t* __restrict__ stage) {
   const uint32_t qaddr = (uint32_t)__cvta_generic_to_shared(queue);
@@ -449,36 +481,33 @@ __device__ __forceinline__ void emit_dense_unit(const Pattern& pat, const ScanAr
   const uint4* __restrict__ mp = a.gran_mask + g0 * 32 + lane;
   unsigned long long base = a.gran_prefix[g0];
   uint64_t pos0 = g0 * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add;
-  uint64_t* __restrict__ outp = a.occ + base + lane;  // this lane's first output slot of the current granule
-  uint4 nxt = __ldg(mp);
+  uint64_t* __restrict__ outp = a.occ + base + lane;  // this lane's first output slot of the current round
+  uint4 nxa = __ldg(mp), nxb = __ldg(mp + 32);
 #pragma unroll 1
-  for (int i = 0; i < 32; ++i) {
-    const uint4 cur = nxt;
-    mp += 32;
-    if (i < 31) nxt = __ldg(mp);
-    const uint32_t c0 = __popc(cur.x), c1 = __popc(cur.y), c2 = __popc(cur.z), c3 = __popc(cur.w);
-    const uint32_t n0 = min(c0, 1u), n1 = min(c1, 1u), n2 = min(c2, 1u), n3 = min(c3, 1u);
-    // one warp scan for both: hits (low half) and non-empty words (high half) before this lane
-    const uint32_t mine = (c0 + c1 + c2 + c3) + ((n0 + n1 + n2 + n3) << 16);
-    const uint32_t inc = warp_inclusive_scan(mine);
-    const uint32_t all = __shfl_sync(kFull, inc, 31);
-    const uint32_t total = all & 0xffffu, qn = all >> 16;
-    const uint32_t excl = inc - mine;
+  for (int i = 0; i < 32; i += 2) {
+    const uint4 ma = nxa, mb = nxb;
+    mp += 64;
+    if (i < 30) {
+      nxa = __ldg(mp);
+      nxb = __ldg(mp + 32);
+    }
+    const uint32_t a0 = __popc(ma.x), a1 = __popc(ma.y), a2 = __popc(ma.z), a3 = __popc(ma.w);
+    const uint32_t b0 = __popc(mb.x), b1 = __popc(mb.y), b2 = __popc(mb.z), b3 = __popc(mb.w);
+    const uint32_t na0 = min(a0, 1u), na1 = min(a1, 1u), na2 = min(a2, 1u), na3 = min(a3, 1u);
+    const uint32_t nb0 = min(b0, 1u), nb1 = min(b1, 1u), nb2 = min(b2, 1u), nb3 = min(b3, 1u);
+    const uint32_t hits = (a0 + a1 + a2 + a3) + ((b0 + b1 + b2 + b3) << 16);      // granule A low, B high
+    const uint32_t nz = (na0 + na1 + na2 + na3) + ((nb0 + nb1 + nb2 + nb3) << 16);
+    const uint32_t inc_h = warp_inclusive_scan(hits), inc_n = warp_inclusive_scan(nz);
+    const uint32_t all_h = __shfl_sync(kFull, inc_h, 31), all_n = __shfl_sync(kFull, inc_n, 31);
+    const uint32_t tot_a = all_h & 0xffffu, total = tot_a + (all_h >> 16);
+    const uint32_t qn_a = all_n & 0xffffu, qn = qn_a + (all_n >> 16);
+    const uint32_t exc_h = inc_h - hits, exc_n = inc_n - nz;
+    const uint32_t slot_a = exc_h & 0xffffu, slot_b = tot_a + (exc_h >> 16);
     if (base + total <= a.occ_cap) {  // (only an estimate-sized list of the non-direct path can be too short)
-      if (total <= kStageCap) {
-        // queue the non-empty words: {mask word, first output slot x 2 (a byte offset into the stage) : position of bit 0}
-        uint32_t q = qaddr + 8 * (excl >> 16);
-        uint32_t tag = ((excl & 0xffffu) << 17) | (uint32_t)(lane * 128);
-        sts64_if(q, cur.x, tag, cur.x);
-        q += 8 * n0;
-        tag += (c0 << 17) + 32u;
-        sts64_if(q, cur.y, tag, cur.y);
-        q += 8 * n1;
-        tag += (c1 << 17) + 32u;
-        sts64_if(q, cur.z, tag, cur.z);
-        q += 8 * n2;
-        tag += (c2 << 17) + 32u;
-        sts64_if(q, cur.w, tag, cur.w);
+      if (total <= 2 * kStageCap) {
+        enqueue_words(ma, a0, a1, a2, na0, na1, na2, qaddr + 8 * (exc_n & 0xffffu), (slot_a << 17) | (uint32_t)(lane * 128));
+        enqueue_words(mb, b0, b1, b2, nb0, nb1, nb2, qaddr + 8 * (qn_a + (exc_n >> 16)),
+                      (slot_b << 17) | (uint32_t)(kGranuleBytes + lane * 128));
         __syncwarp();
 #pragma unroll 1
         for (uint32_t e = lane; e < qn; e += 32) {  // one queued word per lane: at least one hit to place
@@ -508,35 +537,24 @@ __device__ __forceinline__ void emit_dense_unit(const Pattern& pat, const ScanAr
           *o = pos0 + v;
           o += 32;
         }
-        __syncwarp();  // stage and queue are rewritten for the next granule
+        __syncwarp();  // stage and queue are rewritten in the next round
       } else {  // denser than one hit per four bytes: every lane stores its own positions
-        uint64_t* __restrict__ o = outp - lane + (excl & 0xffffu);
-        const uint64_t p = pos0 + (uint32_t)(lane * 128);
-        const uint32_t ws[4] = {cur.x, cur.y, cur.z, cur.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          uint32_t w = ws[k];
-#pragma unroll 1
-          while (w) {
-            const int b = __ffs(w) - 1;
-            w &= w - 1;
-            *o++ = p + (uint32_t)(32 * k + b);
-          }
-        }
+        store_own_positions(ma, outp - lane + slot_a, pos0 + (uint32_t)(lane * 128));
+        store_own_positions(mb, outp - lane + slot_b, pos0 + kGranuleBytes + (uint32_t)(lane * 128));
       }
     }
     base += total;
     outp += total;
-    pos0 += kGranuleBytes;
+    pos0 += 2 * kGranuleBytes;
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 6)
+__global__ void __launch_bounds__(kThreads, 4)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   pdl_wait();
   pdl_trigger();
-  __shared__ uint16_t s_stage[kWarps][kStageCap];
-  __shared__ uint2 s_queue[kWarps][kQueueCap];
+  __shared__ uint16_t s_stage[kWarps][2 * kStageCap];  // (the dense loop stages two granules per round)
+  __shared__ uint2 s_queue[kWarps][2 * kQueueCap];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const uint64_t n_gran = a.n_tiles * kWarps;
