@@ -239,14 +239,16 @@ __global__ void __launch_bounds__(kMaxWorld) summary_kernel(const DevScalars* __
   pdl_trigger();
   unsigned long long v[4];
   v[0] = d->nl_total;
-  v[1] = mode == 1 ? d->occ_total - d->zone_sub + d->zone_add : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
+  v[1] = (mode == 1 || mode == 3) ? d->occ_total - d->zone_sub + d->zone_add
+                                  : (mode == 2 ? d->occ_total - d->drops : d->sel_total[0]);
   v[2] = d->sel_total[1];
   v[3] = want_lines ? d->sel_total[1] - (d->unterminated ? 1 : 0) : 0;
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) out[i] = v[i];
   }
-  const bool redo = (mode == 1 && d->overlap != 0) || (mode == 2 && (d->drops != 0 || d->overlap != 0));
+  const bool redo = (mode == 1 && d->overlap != 0) || (mode == 2 && (d->drops != 0 || d->overlap != 0)) ||
+                    (mode == 3 && d->zone_sub != d->zone_add);
   if (threadIdx.x < pub.world && !redo) {
     ExSlot* slot = pub.peers.table[threadIdx.x] + (pub.round & 1) * pub.world + pub.rank;
 #pragma unroll

@@ -69,7 +69,8 @@ void launch_add_u64(uint64_t* v, uint64_t n, uint64_t delta, cudaStream_t s);
 void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, uint32_t stride, uint32_t rank,
                                cudaStream_t s);
 // summary[0..4) = {newlines, matches, matching lines, lines} from the scan's device scalars
-// mode 0: list path, 1: count-only path (occ_total - zone_sub + zone_add), 2: direct path (occ_total - drops)
+// mode 0: list path, 1: count-only path (occ_total - zone_sub + zone_add), 2: direct path (occ_total - drops),
+// 3: direct path whose tail replay ran list-free on the side stream (zone_sub / zone_add; a difference means redo)
 // pub (may be nullptr): the kernel also stores the summary into every rank's exchange table and releases the round
 // (xsg_exchange.cu) -- unless a fall-back pass will follow (overlap seen / tail drops), whose summary publishes instead
 void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, const ExPublish* pub,

@@ -73,6 +73,9 @@ static int init_ctx(xsg_ctx* c, int device) {
   XSG_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
   c->stream = c->own_stream;
   XSG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  XSG_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
+  XSG_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  XSG_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   for (auto& ev : c->ev) XSG_CUDA(cudaEventCreate(&ev));
   for (int i = 0; i < 2; ++i) {
     XSG_CUDA(cudaEventCreateWithFlags(&c->stage_copied[i], cudaEventDisableTiming));
@@ -170,6 +173,7 @@ void xsg_destroy(xsg_ctx* c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+  if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
   Scratch* all[] = {&c->gran_count, &c->gran_prefix, &c->nl_granule, &c->nl_prefix, &c->scan_tmp, &c->occ,
                     &c->sel, &c->desc2, &c->selq, &c->gran_mask, &c->gran_first, &c->stage[0], &c->stage[1], &c->seg_bounds, &c->stage_bounds[0],
                     &c->stage_bounds[1]};
@@ -189,6 +193,9 @@ void xsg_destroy(xsg_ctx* c) {
   if (c->pool) cudaMemPoolDestroy(c->pool);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   cudaGetLastError();
   delete c;
 }

@@ -38,6 +38,8 @@ struct xsg_ctx {
   cudaStream_t stream = nullptr;       // compute (own_stream unless xsg_set_stream replaced it)
   cudaStream_t own_stream = nullptr;
   cudaStream_t copy_stream = nullptr;  // H2D of streamed segments
+  cudaStream_t aux_stream = nullptr;   // side work of a scan that does not depend on the occurrence list (tail replay)
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   cudaEvent_t ev[6] = {};
   cudaMemPool_t pool = nullptr;        // stream-ordered pool of this context: result vectors
   xsg::Scratch gran_count, gran_prefix, nl_granule, nl_prefix, scan_tmp, occ, sel, desc2, selq, gran_mask, gran_first;
@@ -51,6 +53,7 @@ struct xsg_ctx {
   uint32_t* d_konst = nullptr;           // 12 words: the scan kernel's constants in global memory (see ScanArgs::konst)
   uint32_t* h_konst = nullptr;           // pinned staging of the same (= what d_konst holds once konst_valid)
   bool konst_valid = false;
+  double direct_density = 0;             // occurrences per byte the last direct-mode search saw (sizes the next result vector)
   uint32_t epoch = 0;                    // tag of the look-back descriptors of the next launch (xsg::lookback)
   xsg_exchange* exchange = nullptr;      // the shard exchange attached to this context (xsg_exchange_create), if any
   unsigned int* h_ex_bad = nullptr;      // mapped pinned flag: a wait of the exchange timed out (set by kernels)

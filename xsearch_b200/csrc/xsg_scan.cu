@@ -257,6 +257,19 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     // the list).  So pass 2 writes global offsets straight into the result vector and the list kernels read
     // it with a bias; the select + compact fall-back below covers the exceptions.
     const bool direct = (kinds & XSG_MATCH_BYTE_OFFSETS) != 0;
+    // Direct mode, border-free pattern: what the reference's chunk tails would not report can be counted WITHOUT the
+    // list (zone_count_kernel: the text and the granule counters are all it reads), so that serial, latency-bound
+    // replay -- one warp per reference chunk -- runs on a side stream next to the prefix sums and pass 2 instead of
+    // behind them.
+    const bool zone_aside = direct && !pat.bordered && pat.m > 1 && nb > 0;
+    if (zone_aside) {
+      XSG_CUDA(cudaEventRecord(ctx->ev_fork, s));
+      XSG_CUDA(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+      launch_zone_count(buf, n, d_bounds, nb, pat, a.gran_count, &ds->zone_sub, &ds->zone_add, ctx->aux_stream);
+      XSG_CUDA(cudaGetLastError());
+      XSG_CUDA(cudaEventRecord(ctx->ev_join, ctx->aux_stream));
+      st->launches += 1;
+    }
     launch_exscan2_u32(a.gran_count, ctx->gran_prefix.as<uint64_t>(), &ds->occ_total, a.nl_granule,
                        want_idx ? ctx->nl_prefix.as<uint64_t>() : nullptr, &ds->nl_total, n_gran, scan_desc,
                        &ds->ticket[0], epoch, s);
@@ -270,16 +283,41 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     uint64_t k = 0;
     uint64_t* occ_list = nullptr;
     if (direct) {
-      XSG_CUDA(wait_event(ctx->ev[4]));
-      k = ctx->h_scalars->occ_total;
-      if ((rc = alloc_out(ctx, &part->match_off, k))) return rc;
-      occ_list = part->match_off;
-      a.occ = occ_list;
-      a.occ_cap = k;
+      // The result vector is sized by the exact count, which costs a host round trip with the GPU idle between pass 1
+      // and pass 2.  A context that has searched before (the next segment of a streamed file, the same corpus again)
+      // sizes it from the density the last search saw, 3 % on top, and starts pass 2 at once; if the guess was too
+      // small -- a list that does not fit is simply not written past its capacity -- pass 2 runs again with the
+      // exact size, as it would have anyway.
       a.occ_add = goff;
-      if (k) {
+      const uint64_t guess = ctx->direct_density > 0 ? (uint64_t)(ctx->direct_density * 1.03 * (double)n) + 4096 : 0;
+      bool emitted = false;
+      if (guess) {
+        if ((rc = alloc_out(ctx, &part->match_off, guess))) return rc;
+        a.occ = part->match_off;
+        a.occ_cap = guess;
         XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
         st->launches += 1;
+        emitted = true;
+      }
+      XSG_CUDA(wait_event(ctx->ev[4]));
+      k = ctx->h_scalars->occ_total;
+      ctx->direct_density = (double)k / (double)n;
+      if (emitted && k > guess) {
+        XSG_CUDA(cudaFreeAsync(part->match_off, s));
+        part->match_off = nullptr;
+        emitted = false;
+      }
+      if (!emitted) {
+        if ((rc = alloc_out(ctx, &part->match_off, k))) return rc;
+        a.occ = part->match_off;
+        a.occ_cap = k;
+        if (k) {
+          XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+          st->launches += 1;
+        }
+      }
+      occ_list = part->match_off;
+      if (k) {
         if (pat.bordered) {
           launch_overlap_check(occ_list, k, pat.m, &ds->overlap, s);
           st->launches += 1;
@@ -317,10 +355,12 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         if (fam == 0 ? !want_match : !want_line) continue;
         const int mode = fam == 1 ? kSelLine : (pat.bordered ? kSelMatchBordered : kSelMatch);
         if (fam == 0 && direct) {  // only count what the reference's chunk tails would not report
-          ListArgs ld = l;
-          ld.sel = nullptr;
-          launch_zone(ld, pat, kSelMatch, s);  // bordered: meaningful only if nothing overlaps (else fall-back)
-          st->launches += pat.m > 1 ? 1 : 0;
+          if (!zone_aside) {
+            ListArgs ld = l;
+            ld.sel = nullptr;
+            launch_zone(ld, pat, kSelMatch, s);  // bordered: meaningful only if nothing overlaps (else fall-back)
+            st->launches += pat.m > 1 ? 1 : 0;
+          }
           continue;
         }
         st->launches += launch_select_zone(l, pat, mode, s);
@@ -365,11 +405,13 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         st->launches += c.selq ? 2 : 1;
       }
     }
-    launch_summary(ds, direct ? 2 : 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s);
+    if (zone_aside) XSG_CUDA(cudaStreamWaitEvent(s, ctx->ev_join, 0));
+    launch_summary(ds, zone_aside ? 3 : (direct ? 2 : 0), (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s);
     st->launches += 1;
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
-    if (direct && k > 0 && (ctx->h_scalars->drops || ctx->h_scalars->overlap)) {
+    if (direct && k > 0 &&
+        (ctx->h_scalars->drops || ctx->h_scalars->overlap || (zone_aside && ctx->h_scalars->zone_sub != ctx->h_scalars->zone_add))) {
       // a chunk tail of the reference skipped occurrences, or occurrences overlap (greedy selection needed):
       // select + compact the list into a new vector
       const int fb_mode = pat.bordered ? kSelMatchBordered : kSelMatch;
