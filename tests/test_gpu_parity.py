@@ -27,10 +27,19 @@ def ctx(xs):
     c.close()
 
 
-@pytest.fixture(scope="module")
-def oracle():
-    o, _ = oracle_lib.load(build=False)
-    return o
+@pytest.fixture(scope="module", params=["restatement", "reference"])
+def oracle(request):
+    """Every parity test runs twice: against the C restatement (oracle/libxsoracle.so) and -- VERDICT r1 #7 -- directly
+    against the reference's own sources (oracle/_ref/libxsref.so, which travels to the GPU box with the snapshot)."""
+    o, ref = oracle_lib.load(build=False)
+    if request.param == "restatement":
+        return o
+    if ref is None:
+        pytest.skip("oracle/_ref/libxsref.so is not built")
+    if not hasattr(ref, "_chunk_from"):
+        ref.chunk_bounds = o.chunk_bounds  # v1 chunking is harness code (the reference snapshot lacks it)
+        ref._chunk_from = "restatement"
+    return ref
 
 
 def all_kinds(xs):
@@ -425,6 +434,25 @@ def test_full_size_properties_10gb(xs, ctx):
     assert cnt == whole["count"] and cl == whole["cl"] and line_base == whole["nl"]
     for k in parts:
         assert np.array_equal(np.concatenate(parts[k]), whole[k]), k
+    # (4) at this size too: element by element against the reference's own code (oracle/_ref/libxsref.so travels to the
+    # GPU box; the C restatement otherwise), all host cores, when the box has the memory for a host copy of the corpus
+    try:
+        avail = int(next(l for l in open("/proc/meminfo") if l.startswith("MemAvailable")).split()[1]) * 1024
+    except Exception:
+        avail = 0
+    if avail > 3 * n:
+        restatement, ref = oracle_lib.load(build=False)
+        chk = ref or restatement
+        host = corpus.download()
+        threads = os.cpu_count() or 1
+        assert chk.count(host, b"Sherlock", bounds, False, threads) == whole["count"]
+        assert chk.count(host, b"Sherlock", bounds, True, threads) == whole["cl"]
+        assert np.array_equal(chk.match_byte_offsets(host, b"Sherlock", bounds, threads), whole["m"])
+        assert np.array_equal(chk.line_byte_offsets(host, b"Sherlock", bounds, threads), whole["lo"])
+        assert np.array_equal(chk.line_indices(host, b"Sherlock", bounds, threads), whole["li"])
+        es, el = chk.lines(host, b"Sherlock", bounds, threads)
+        assert np.array_equal(es, whole["ls"][0]) and np.array_equal(el, whole["ls"][1])
+        del host
     # dense direct path vs the list-free count path
     r = ctx.scan(corpus, b"the", xs.MATCH_BYTE_OFFSETS | xs.COUNT)
     c_list, v = r.count(xs.COUNT), r.vector(xs.MATCH_BYTE_OFFSETS)
@@ -568,3 +596,29 @@ def test_stream_interface_parts_and_errors(xs, ctx, oracle):
     st.abort()
     with pytest.raises(xs.XsgError):
         xs.Stream(ctx, b"a\nb", xs.COUNT)
+
+
+def test_same_pattern_again_with_changing_density(xs, ctx, oracle):
+    """A context that has searched before sizes the result vector of match_byte_offsets from the density the previous
+    search saw, before the count of this one is back on the host (xsg_scan.cu: direct_density): the guess is too small
+    when the density rises, far too large when it falls to zero -- the results must not care."""
+    line_kinds = xs.COUNT_LINES | xs.LINE_BYTE_OFFSETS | xs.LINE_INDICES | xs.LINES
+    for step, rate in enumerate((30.0 / 65536, 30.0 / 2048, 0.0, 30.0 / 512, 30.0 / 65536, 30.0 / 65536)):
+        buf = xs.synth_host(4096 * 700, xs.SynthParams.make(70 + step, b"Sherlock", rate))
+        bounds = xs.chunk_bounds_host(buf, 1 << 18)
+        exp = expected(oracle, buf, b"Sherlock", bounds)
+        corpus = ctx.corpus_from_host(buf, bounds=bounds)
+        try:
+            for _ in range(2):
+                res = ctx.scan(corpus, b"Sherlock", line_kinds)
+                assert res.count(xs.COUNT_LINES) == exp["count_lines"], (step, rate)
+                assert np.array_equal(res.vector(xs.LINE_BYTE_OFFSETS), exp["line_off"]), (step, rate)
+                assert np.array_equal(res.vector(xs.LINE_INDICES), exp["line_idx"]), (step, rate)
+                st, ln = res.line_spans()
+                assert np.array_equal(st, exp["lines"][0]) and np.array_equal(ln, exp["lines"][1]), (step, rate)
+                res.free()
+                res = ctx.scan(corpus, b"Sherlock", xs.MATCH_BYTE_OFFSETS)
+                assert np.array_equal(res.vector(xs.MATCH_BYTE_OFFSETS), exp["match"]), (step, rate)
+                res.free()
+        finally:
+            corpus.free()
