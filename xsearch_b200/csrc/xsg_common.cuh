@@ -81,9 +81,7 @@ struct ListArgs {
   const uint64_t* bounds;  // device: exclusive chunk ends
   uint64_t nb;
   const uint64_t* occ;     // sorted raw occurrences
-  uint64_t k;              // number of raw occurrences (an upper bound when k_dev is set)
-  const unsigned long long* k_dev;  // nullptr, or where the device holds the true number: a list stage launched before
-                                    // the host knew it (sized by a guess) works on min(k, *k_dev) entries
+  uint64_t k;              // number of raw occurrences
   uint8_t* sel;            // [k] selection flags (output of select / zone kernels)
   const uint64_t* gran_prefix;  // [n_gran + 1] exclusive prefix of the granule counts (brackets searches in occ) or nullptr
   uint64_t n_gran;
