@@ -97,7 +97,10 @@ struct Options {
   // only; a regular expression runs on devices[0].  Empty: {device}.
   std::vector<int> devices;
   uint64_t min_chunk = XSG_DEFAULT_MIN_CHUNK;   // v1: chunks of >= 16 MiB, extended through the next '\n'
-  uint64_t segment_bytes = 256ull << 20;        // bytes read / copied / scanned per pipeline step
+  // bytes read / copied / scanned per pipeline step.  64 MiB: the first H2D copy starts after 2 ms of reading and
+  // the pinned buffers are small (81 MB each); measured on an 8 GiB file, 16 readers: 41.3 GB/s against 39.8 (128 MiB),
+  // 37.1 (256 MiB), 31 (512 MiB) -- repo:profiles/r2_file_segment_sweep.txt
+  uint64_t segment_bytes = 64ull << 20;
   bool ignore_case = false;                     // set by the ignore_case overloads of extern_search
   // AUTO = the reference's rule (xs::use_str_as_regex, utils.h:17-24); LITERAL / REGEX force one reading
   enum class PatternMode { AUTO, LITERAL, REGEX };
