@@ -438,6 +438,96 @@ __device__ __forceinline__ void expand_queued(const GranMask& cur, uint32_t hits
   __syncwarp();
 }
 
+// The dense unit, one granule per round (the variant of emit_kernel that keeps its shared memory small, below).
+__device__ __forceinline__ void emit_dense_unit1(const Pattern& pat, const ScanArgs& a, uint64_t g0, int lane,
+                                                uint2* __restrict__ queue, uint16_t* __restrict__ stage) {
+  const uint32_t qaddr = (uint32_t)__cvta_generic_to_shared(queue);
+  const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(stage);
+  const uint4* __restrict__ mp = a.gran_mask + g0 * 32 + lane;
+  unsigned long long base = a.gran_prefix[g0];
+  uint64_t pos0 = g0 * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add;
+  uint64_t* __restrict__ outp = a.occ + base + lane;  // this lane's first output slot of the current granule
+  uint4 nxt = __ldg(mp);
+#pragma unroll 1
+  for (int i = 0; i < 32; ++i) {
+    const uint4 cur = nxt;
+    mp += 32;
+    if (i < 31) nxt = __ldg(mp);
+    const uint32_t c0 = __popc(cur.x), c1 = __popc(cur.y), c2 = __popc(cur.z), c3 = __popc(cur.w);
+    const uint32_t n0 = min(c0, 1u), n1 = min(c1, 1u), n2 = min(c2, 1u), n3 = min(c3, 1u);
+    // one warp scan for both: hits (low half) and non-empty words (high half) before this lane
+    const uint32_t mine = (c0 + c1 + c2 + c3) + ((n0 + n1 + n2 + n3) << 16);
+    const uint32_t inc = warp_inclusive_scan(mine);
+    const uint32_t all = __shfl_sync(kFull, inc, 31);
+    const uint32_t total = all & 0xffffu, qn = all >> 16;
+    const uint32_t excl = inc - mine;
+    if (base + total <= a.occ_cap) {  // (only an estimate-sized list of the non-direct path can be too short)
+      if (total <= kStageCap) {
+        // queue the non-empty words: {mask word, first output slot x 2 (a byte offset into the stage) : position of bit 0}
+        uint32_t q = qaddr + 8 * (excl >> 16);
+        uint32_t tag = ((excl & 0xffffu) << 17) | (uint32_t)(lane * 128);
+        sts64_if(q, cur.x, tag, cur.x);
+        q += 8 * n0;
+        tag += (c0 << 17) + 32u;
+        sts64_if(q, cur.y, tag, cur.y);
+        q += 8 * n1;
+        tag += (c1 << 17) + 32u;
+        sts64_if(q, cur.z, tag, cur.z);
+        q += 8 * n2;
+        tag += (c2 << 17) + 32u;
+        sts64_if(q, cur.w, tag, cur.w);
+        __syncwarp();
+#pragma unroll 1
+        for (uint32_t e = lane; e < qn; e += 32) {  // one queued word per lane: at least one hit to place
+          uint32_t w, t;
+          asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w), "=r"(t) : "r"(qaddr + 8 * e));
+          const uint32_t bpos = t & 0xffffu;
+          const uint32_t dst = saddr + (t >> 16);
+          sts16_if<0>(dst, bpos + __ffs(w) - 1, 1u);
+          w &= w - 1;
+          sts16_if<2>(dst, bpos + __ffs(w) - 1, w);
+          w &= w - 1;
+          uint32_t d = dst + 4;
+#pragma unroll 1
+          while (w) {  // three and more hits in four bytes of text: rare
+            sts16_if<0>(d, bpos + __ffs(w) - 1, 1u);
+            w &= w - 1;
+            d += 2;
+          }
+        }
+        __syncwarp();
+        // coalesced write-out: 32 consecutive offsets per store instruction
+        uint64_t* __restrict__ o = outp;
+#pragma unroll 1
+        for (uint32_t j = lane; j < total; j += 32) {
+          uint32_t v;
+          asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(saddr + 2 * j));
+          *o = pos0 + v;
+          o += 32;
+        }
+        __syncwarp();  // stage and queue are rewritten for the next granule
+      } else {  // denser than one hit per four bytes: every lane stores its own positions
+        uint64_t* __restrict__ o = outp - lane + (excl & 0xffffu);
+        const uint64_t p = pos0 + (uint32_t)(lane * 128);
+        const uint32_t ws[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint32_t w = ws[k];
+#pragma unroll 1
+          while (w) {
+            const int b = __ffs(w) - 1;
+            w &= w - 1;
+            *o++ = p + (uint32_t)(32 * k + b);
+          }
+        }
+      }
+    }
+    base += total;
+    outp += total;
+    pos0 += kGranuleBytes;
+  }
+}
+
 // A unit whose 32 granules ALL hold two or more occurrences (a frequent short pattern): no search for the next hit
 // granule, no per-granule base from a shuffle -- the output of the unit is one contiguous run, so the base just
 // advances by every round's total -- and 32-bit shared-memory addresses and pointer increments throughout: this
@@ -549,12 +639,17 @@ __device__ __forceinline__ void emit_dense_unit(const Pattern& pat, const ScanAr
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 4)
+// PAIRS: the dense loop takes two granules per round and the kernel carries 48 KiB of shared memory (4 CTAs per SM) --
+// right when most granules hold several occurrences, which only direct mode knows at launch time.  Otherwise: 24 KiB,
+// 6 CTAs per SM -- a sparse search is a few waves of latency-bound warps and wants them resident (35 -> 25 us on the
+// headline workload).
+template <bool PAIRS>
+__global__ void __launch_bounds__(kThreads, PAIRS ? 4 : 6)
 emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
   pdl_wait();
   pdl_trigger();
-  __shared__ uint16_t s_stage[kWarps][2 * kStageCap];  // (the dense loop stages two granules per round)
-  __shared__ uint2 s_queue[kWarps][2 * kQueueCap];
+  __shared__ uint16_t s_stage[kWarps][(PAIRS ? 2 : 1) * kStageCap];
+  __shared__ uint2 s_queue[kWarps][(PAIRS ? 2 : 1) * kQueueCap];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const uint64_t n_gran = a.n_tiles * kWarps;
@@ -570,7 +665,8 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   unsigned todo = __ballot_sync(kFull, c > 1);
   if (todo == 0) return;
   if (todo == kFull) {  // every granule of the unit holds several occurrences: the dense case, as a straight loop
-    emit_dense_unit(pat, a, g0, lane, s_queue[warp], s_stage[warp]);
+    if (PAIRS) emit_dense_unit(pat, a, g0, lane, s_queue[warp], s_stage[warp]);
+    else emit_dense_unit1(pat, a, g0, lane, s_queue[warp], s_stage[warp]);
     return;
   }
   // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below).  The
@@ -675,12 +771,12 @@ cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, b
   return pat.icase ? launch_count_ic<true>(pat, a, newlines, masks, s) : launch_count_ic<false>(pat, a, newlines, masks, s);
 }
 
-cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s) {
+cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, bool dense, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
-  (void)sm_count;
   const uint64_t units = div_up(a.n_tiles * kWarps, 32);  // units of 32 granules, one warp each
   const dim3 grid((unsigned)div_up(units, kWarps)), block(kThreads);
-  launch_dependent(emit_kernel, grid, block, s, pat, a);
+  if (dense) launch_dependent(emit_kernel<true>, grid, block, s, pat, a);
+  else launch_dependent(emit_kernel<false>, grid, block, s, pat, a);
   return cudaGetLastError();
 }
 

@@ -72,7 +72,8 @@ struct ScanArgs {
 
 // launchers implemented in scan_kernel.cu
 cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s);  // pat.icase selects the folding variant
-cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, int sm_count, cudaStream_t s);
+// dense: most granules hold several occurrences (known in direct mode): the variant with two granules per round
+cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, bool dense, cudaStream_t s);
 
 // ---- list-domain (post) kernels, list_kernels.cu -------------------------------------------
 struct ListArgs {

@@ -295,7 +295,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         if ((rc = alloc_out(ctx, &part->match_off, guess))) return rc;
         a.occ = part->match_off;
         a.occ_cap = guess;
-        XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+        XSG_CUDA(launch_emit(pat, a, guess > 4 * n_gran, s));
         st->launches += 1;
         emitted = true;
       }
@@ -312,7 +312,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         a.occ = part->match_off;
         a.occ_cap = k;
         if (k) {
-          XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+          XSG_CUDA(launch_emit(pat, a, k > 4 * n_gran, s));
           st->launches += 1;
         }
       }
@@ -329,7 +329,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       if ((rc = ctx->occ.reserve(cap * sizeof(uint64_t)))) return rc;
       a.occ = ctx->occ.as<uint64_t>();
       a.occ_cap = cap;
-      XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));  // the count travels to the host while this runs
+      XSG_CUDA(launch_emit(pat, a, false, s));  // the count travels to the host while this runs
       st->launches += 1;
       XSG_CUDA(wait_event(ctx->ev[4]));
       k = ctx->h_scalars->occ_total;
@@ -338,7 +338,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
         if ((rc = ctx->occ.reserve(k * sizeof(uint64_t)))) return rc;
         a.occ = ctx->occ.as<uint64_t>();
         a.occ_cap = k;
-        XSG_CUDA(launch_emit(pat, a, ctx->sm_count, s));
+        XSG_CUDA(launch_emit(pat, a, false, s));
         st->launches += 1;
       }
       occ_list = ctx->occ.as<uint64_t>();
