@@ -131,10 +131,10 @@ __device__ __forceinline__ uint32_t verify_row(const Pattern& pat, const uint8_t
 #endif
 constexpr bool kPairRows = XSG_PAIR_ROWS != 0;
 
-template <int NS, bool EMIT, bool NL, bool ICASE, bool OVL>
+template <int NS, bool EMIT, bool NL, bool ICASE, bool OVL, bool STAGED = false>
 __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8_t* __restrict__ buf, uint64_t n,
                                                  uint64_t gran_off, int lane, const uint4 (&v)[kRows], uint32_t ext,
-                                                 const uint4* __restrict__ konst, LaneResult& r) {
+                                                 const uint4* __restrict__ konst, LaneResult& r, uint32_t srow = 0) {
   const uint64_t lane_off = gran_off + (uint64_t)lane * 16;
   const bool partial = gran_off + kGranuleBytes + 16 > n;
 
@@ -163,10 +163,16 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
     // <=> (b | 0x20) == c, and for any other c <=> b == c.  The per-byte OR mask (pat.orm[k]: 0x20 in every
     // lane if pattern byte k is a letter, else 0) rides along in the LOP3 that does the compare.
     const uint32_t w0 = v[u].x, w1 = v[u].y, w2 = v[u].z, w3 = v[u].w;
-    // halo word: lane l takes word 0 of lane l+1; lane 31 takes word 0 of the next row (held by lane 0)
-    uint32_t send = w0;
-    if (lane == 0) send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
-    const uint32_t w4 = __shfl_sync(kFull, send, (lane + 1) & 31);
+    // halo word: lane l takes word 0 of lane l+1; lane 31 takes word 0 of the next row (held by lane 0).
+    // STAGED (the tile sits in shared memory, count_kernel_staged): it is simply the next word there.
+    uint32_t w4;
+    if (STAGED) {
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w4) : "r"(srow + u * kRowBytes + 16));
+    } else {
+      uint32_t send = w0;
+      if (lane == 0) send = (u < kRows - 1) ? v[(u < kRows - 1) ? u + 1 : u].x : ext;
+      w4 = __shfl_sync(kFull, send, (lane + 1) & 31);
+    }
     const uint64_t pos0 = lane_off + (uint64_t)u * kRowBytes;
 
     if (NL) {  // 128 x (bytes that are not '\n'), accumulated on the multiply-add pipe
@@ -296,13 +302,22 @@ __device__ __forceinline__ void classify_granule(const Pattern& pat, const uint8
 // No inter-warp communication at all: each warp owns its granule and writes its own counters.  With
 // MASK the 512-byte occurrence bitmask of a granule is stored when (and only when) the granule holds
 // an occurrence, so pass 2 never touches the corpus again.
-template <int NS, bool NL, bool MASK, bool ICASE, bool OVL>
-__device__ __forceinline__ bool count_tile(const Pattern& pat, const ScanArgs& a, uint64_t tile, int lane, int warp) {
+template <int NS, bool NL, bool MASK, bool ICASE, bool OVL, bool STAGED = false>
+__device__ __forceinline__ bool count_tile(const Pattern& pat, const ScanArgs& a, uint64_t tile, int lane, int warp,
+                                           uint32_t stile = 0) {
   const uint64_t g = tile * kWarps + warp;
   const uint64_t gran_off = g * (uint64_t)kGranuleBytes;
   uint4 v[kRows];
-  uint32_t ext;
-  load_granule(a.buf, a.n, gran_off, lane, v, ext);
+  uint32_t ext = 0;
+  const uint32_t srow = stile + (uint32_t)warp * kGranuleBytes + (uint32_t)lane * 16;  // this lane's 16 bytes of row 0
+  if (STAGED) {  // bytes behind n were zeroed in shared memory: no masking here
+#pragma unroll
+    for (int u = 0; u < kRows; ++u)
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "r"(srow + u * kRowBytes));
+  } else {
+    load_granule(a.buf, a.n, gran_off, lane, v, ext);
+  }
   if (OVL) {
     // give up once any CTA has seen an overlap (see count_kernel).  The flag is read behind the granule
     // loads, so its latency hides under theirs; the loads of this one tile are all an aborted pass wastes.
@@ -311,7 +326,7 @@ __device__ __forceinline__ bool count_tile(const Pattern& pat, const ScanArgs& a
     if (seen != 0) return true;
   }
   LaneResult r;
-  classify_granule<NS, MASK, NL, ICASE, OVL>(pat, a.buf, a.n, gran_off, lane, v, ext, a.konst, r);
+  classify_granule<NS, MASK, NL, ICASE, OVL, STAGED>(pat, a.buf, a.n, gran_off, lane, v, ext, a.konst, r, srow);
   if (OVL && r.ovl != 0) *a.overlap = 1u;
   if (NL) {
     // '\n' per half of the granule, both counts in ONE warp reduction (a lane holds 64 bytes of each half)
@@ -358,6 +373,51 @@ count_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanAr
   // tile-per-CTA grid would still have to drain a million empty CTAs).
   for (uint64_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
     if (count_tile<NS, NL, MASK, ICASE, OVL>(pat, a, tile, lane, warp)) return;
+}
+
+// ---- EXPERIMENT (north_star: "shared-memory (or TMA) staging of chunk tiles plus a pattern-length halo"): the CTA's
+// 32 KiB tile + 16 halo bytes arrive in shared memory by ONE bulk async copy (cp.async.bulk, completion on an mbarrier;
+// SASS: UBLKCP), the warps then read their rows with ld.shared.v4 and the halo word with ld.shared.u32 instead of a
+// shuffle + select; bytes behind n are zeroed in shared memory.  Built for the exact-compare variants (m <= 4), which
+// are bound by the ALU pipe: the question is whether taking the 64-bit address arithmetic, the ragged-tile masking and
+// the halo select off that pipe pays for the extra trip through shared memory.  XSG_STAGED=1 selects it; the number
+// is in DESIGN.md 8.
+template <int NS, bool NL, bool MASK, bool ICASE>
+__global__ void __launch_bounds__(kThreads, 3)
+count_kernel_staged(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArgs a) {
+  extern __shared__ __align__(128) uint8_t s_tile[];  // kTileBytes + 16 halo bytes, then the mbarrier
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  pdl_trigger();
+  const uint32_t stile = (uint32_t)__cvta_generic_to_shared(s_tile);
+  const uint32_t bar = stile + kTileBytes + 16;
+  const uint64_t off = (uint64_t)blockIdx.x * kTileBytes;
+  const uint64_t readable = (a.n + 15) & ~15ull;  // the corpus is readable up to the next 16-byte boundary
+  const uint32_t bytes = (uint32_t)(readable - off < kTileBytes + 16 ? readable - off : kTileBytes + 16);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(stile), "l"(a.buf + off), "r"(bytes), "r"(bar) : "memory");
+  }
+  // what the copy does not fill (ragged last tile) and the bytes behind n: zero
+  const uint64_t valid = a.n - off < kTileBytes + 16 ? a.n - off : kTileBytes + 16;
+  if (bytes < kTileBytes + 16)
+    for (uint32_t i = bytes + threadIdx.x; i < kTileBytes + 16; i += kThreads) s_tile[i] = 0;
+  uint32_t done = 0;
+  while (!done)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar) : "memory");
+  if (valid < bytes) {  // readable but behind n (at most 15 bytes)
+    __syncthreads();
+    if (threadIdx.x < bytes - valid) s_tile[valid + threadIdx.x] = 0;
+  }
+  if (bytes < kTileBytes + 16 || valid < bytes) __syncthreads();
+  count_tile<NS, NL, MASK, ICASE, false, true>(pat, a, blockIdx.x, lane, warp, stile);
 }
 
 // ---- pass 2: ordered emission from the stored masks.  The output position of a granule is the
@@ -734,6 +794,11 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   }
 }
 
+inline bool staged_enabled() {
+  static const bool on = std::getenv("XSG_STAGED") != nullptr;
+  return on;
+}
+
 template <int NS, bool ICASE>
 cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines, bool masks, cudaStream_t s) {
   const dim3 grid((unsigned)a.n_tiles), block(kThreads);
@@ -741,6 +806,13 @@ cudaError_t launch_count_ns(const Pattern& pat, const ScanArgs& a, bool newlines
     const dim3 strided((unsigned)(a.n_tiles < 148u * 4 * 4 ? a.n_tiles : 148u * 4 * 4));
     if (NS <= 4) count_kernel<(NS <= 4 ? NS : 1), false, false, ICASE, true><<<strided, block, 0, s>>>(pat, a);
     else return cudaErrorInvalidValue;
+  } else if (NS <= 4 && staged_enabled()) {
+    constexpr int N4 = NS <= 4 ? NS : 1;
+    const size_t smem = kTileBytes + 16 + 16;
+    if (masks && newlines) count_kernel_staged<N4, true, true, ICASE><<<grid, block, smem, s>>>(pat, a);
+    else if (masks) count_kernel_staged<N4, false, true, ICASE><<<grid, block, smem, s>>>(pat, a);
+    else if (newlines) count_kernel_staged<N4, true, false, ICASE><<<grid, block, smem, s>>>(pat, a);
+    else count_kernel_staged<N4, false, false, ICASE><<<grid, block, smem, s>>>(pat, a);
   } else if (masks) {
     if (newlines) count_kernel<NS, true, true, ICASE><<<grid, block, 0, s>>>(pat, a);
     else count_kernel<NS, false, true, ICASE><<<grid, block, 0, s>>>(pat, a);
