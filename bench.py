@@ -624,9 +624,8 @@ def run_ours(args):
                                "mean of 2, CUDA events, max over ranks" % world,
                "path": "xsg_search_host: pinned host buffer -> double-buffered H2D segments -> scan -> D2H of results"}
         if results == 0 and streamed is not None:
-            results = int(sum_over_ranks(result_count(streamed[tags[-1]]) if not isinstance(streamed[tags[-1]], (int, tuple))
-                                         else (streamed[tags[-1]] if isinstance(streamed[tags[-1]], int)
-                                               else streamed[tags[-1]][0].size)))
+            v = streamed[tags[-1]]
+            results = int(sum_over_ranks(v if isinstance(v, int) else (v[0].size if isinstance(v, tuple) else v.size)))
 
     # ---- parity + cpu_baseline: the reference's matchers on the SAME bytes, results compared ------------
     parity = None
