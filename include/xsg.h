@@ -244,6 +244,26 @@ int xsg_exchange_totals(xsg_exchange* x, uint64_t* table_host /* world x 4 */);
 int xsg_exchange_check(xsg_exchange* x); /* synchronizes the context's stream; XSG_ERR_STATE after a timed-out wait */
 void xsg_exchange_destroy(xsg_exchange* x);
 
+/* ---- xs::count without any allocation --------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The list-free count path of xsg_scan(kinds = XSG_COUNT) with its scratch memory -- one u32 per 4 KiB of text, the
+ * scan's constants and scalars -- in a fixed __device__ array inside libxsg.so (1 MiB + 512 B, held by every GPU that
+ * loads the library until the process exits) instead of the context's cudaMalloc'ed buffers.  The call allocates
+ * nothing, needs no xsg_ctx, launches its kernels on `cuda_stream` of `device` (which it makes current) and returns
+ * without synchronizing; in stream order d_out[0] = the reference's xs::count over the chunks d_bounds[0..nb)
+ * (exclusive chunk ends on the device, as for xsg_corpus_set_bounds; NULL = the whole text is one chunk) and
+ * d_out[1] = OR of XSG_STATIC_* flags (0 = d_out[0] is valid).  d_text: device memory, 16-byte aligned, readable up to
+ * the next 16-byte boundary.  flags: 0 or XSG_SCAN_IGNORE_CASE.
+ * Limits: n <= XSG_STATIC_SCRATCH_MAX_TEXT, else XSG_ERR_ARG (split the text at chunk bounds and add the counts, or
+ * use xsg_scan); a self-overlapping pattern of more than 4 bytes is XSG_ERR_ARG (it needs the occurrence list).
+ * Every call on a device shares the one array: calls that overlap on the GPU (two streams, two threads) race. */
+#define XSG_STATIC_SCRATCH_MAX_TEXT (1ull << 30)
+#define XSG_STATIC_OVERLAP 1u    /* occurrences of a self-overlapping pattern overlap in this text: use xsg_scan */
+#define XSG_STATIC_BAD_BOUNDS 2u /* d_bounds not increasing / not newline-aligned / not ending at n             */
+int xsg_count_static_scratch(int device, void* cuda_stream, const void* d_text, uint64_t n, const uint64_t* d_bounds,
+                             uint64_t nb, const uint8_t* pattern, uint32_t m, uint32_t flags, uint64_t* d_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -87,3 +87,18 @@ def test_init_fails_loudly_without_gpu():
     with pytest.raises(xs.XsgError) as e:
         xs.Context(0)
     assert "no CPU fallback" in str(e.value)
+
+
+def test_static_scratch_entry_checks_arguments_before_touching_cuda():
+    """xsg_count_static_scratch: the size limit and the pattern rules are host-side checks (clear errors, no GPU needed);
+    with valid arguments and no GPU it fails loudly like every compute entry point."""
+    import torch
+    out = (C.c_uint64 * 2)()
+    call = lambda n, pat: xs.lib.xsg_count_static_scratch(0, None, C.c_void_p(4096), n, None, 0, pat, len(pat), 0,
+                                                          C.cast(out, C.c_void_p))
+    assert call(xs.STATIC_SCRATCH_MAX_TEXT + 1, b"Sherlock") == -2
+    assert "exceeds the static scratch's maximum of %d bytes" % xs.STATIC_SCRATCH_MAX_TEXT in xs.lib.xsg_last_error().decode()
+    assert call(4096, b"abcabcab") == -2 and "occurrence list" in xs.lib.xsg_last_error().decode()
+    assert call(4096, b"") == -2
+    if not torch.cuda.is_available():
+        assert call(4096, b"Sherlock") == -1  # XSG_ERR_CUDA

@@ -31,6 +31,9 @@ LINES = 1 << 5
 SCAN_IGNORE_CASE = 1  # xsg_scan_opts.flags
 SCAN_PUBLISH = 2
 SCAN_LOCAL_LINE_INDEX = 4
+STATIC_SCRATCH_MAX_TEXT = 1 << 30  # xsg_count_static_scratch
+STATIC_OVERLAP = 1
+STATIC_BAD_BOUNDS = 2
 
 # the reference's tag names (README.md:72-81; tests also spell xs::count as count_matches)
 TAGS = {
@@ -55,7 +58,7 @@ EXPORTS = [
     "xsg_result_copy", "xsg_result_copy_line_lengths", "xsg_result_device_ptr", "xsg_result_newlines",
     "xsg_result_raw_occurrences", "xsg_result_timings", "xsg_result_rebase", "xsg_scan_summary_device", "xsg_result_rebase_from_table", "xsg_result_free",
     "xsg_exchange_create", "xsg_exchange_connect", "xsg_exchange_connect_local", "xsg_exchange_check", "xsg_exchange_push", "xsg_result_rebase_exchanged", "xsg_exchange_totals",
-    "xsg_exchange_destroy",
+    "xsg_exchange_destroy", "xsg_count_static_scratch",
 ]
 
 
@@ -157,6 +160,7 @@ def _load() -> C.CDLL:
         "xsg_result_rebase_exchanged": (i32, [vp, vp]),
         "xsg_exchange_totals": (i32, [vp, pu64]),
         "xsg_exchange_destroy": (None, [vp]),
+        "xsg_count_static_scratch": (i32, [i32, vp, vp, u64, vp, u64, C.c_char_p, u32, u32, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

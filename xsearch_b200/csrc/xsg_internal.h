@@ -12,6 +12,8 @@ namespace xsg {
 
 void set_error(const std::string& msg);
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+// validated, preprocessed pattern (xsg_scan.cu: filter bytes, borders, fold masks)
+int build_pattern(const uint8_t* p, uint32_t m, bool icase, Pattern* out);
 
 #define XSG_CUDA(expr)                                                    \
   do {                                                                    \

@@ -474,4 +474,9 @@ void finish_result(xsg_result* r, const ScanStats& st) {
 
 }  // namespace
 
+namespace xsg {
+// make_pattern for the other translation units (xsg_static_scratch.cu)
+int build_pattern(const uint8_t* p, uint32_t m, bool icase, Pattern* out) { return make_pattern(p, m, icase, out); }
+}  // namespace xsg
+
 #include "xsg_scan_api.inc"
