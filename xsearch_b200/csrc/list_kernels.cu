@@ -134,6 +134,7 @@ struct Scan2 {
   const uint32_t* in[2];
   uint64_t* out[2];
   unsigned long long* total[2];
+  unsigned long long* host_total;  // mapped host memory: the total of table 0 goes there as well (or nullptr)
 };
 
 // Single pass (decoupled look-back between the tiles of a table): a tile of 8192 counters is read once, its
@@ -181,7 +182,10 @@ __global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_const
     const unsigned long long excl = lookback(desc_all + (uint64_t)blockIdx.y * nblk, tile, total, threadIdx.x, epoch);
     if (threadIdx.x == 0) {
       s_base = excl;
-      if (tile + 1 == nblk) *a.total[blockIdx.y] = excl + total;
+      if (tile + 1 == nblk) {
+        *a.total[blockIdx.y] = excl + total;
+        if (blockIdx.y == 0 && a.host_total) *a.host_total = excl + total;  // the host reads it behind an event: no copy
+      }
     }
   }
   __syncthreads();
@@ -234,9 +238,11 @@ __global__ void __launch_bounds__(256) overlap_check_kernel(const uint64_t* __re
 // launch of its own.  A pass that will be redone (the list-free count saw overlapping occurrences; the direct path
 // saw tail drops or overlaps) publishes nothing: the summary of the fall-back pass does.
 __global__ void __launch_bounds__(kMaxWorld) summary_kernel(const DevScalars* __restrict__ d, int mode, int want_lines,
-                                                           unsigned long long* out, const __grid_constant__ ExPublish pub) {
+                                                           unsigned long long* out, const __grid_constant__ ExPublish pub,
+                                                           DevScalars* mirror) {
   pdl_wait();
   pdl_trigger();
+  if (mirror && threadIdx.x == 0) *mirror = *d;  // mapped host memory: the host reads the scalars behind the scan's last event
   unsigned long long v[4];
   v[0] = d->nl_total;
   v[1] = (mode == 1 || mode == 3) ? d->occ_total - d->zone_sub + d->zone_add
@@ -266,11 +272,11 @@ void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned 
 }
 
 void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, const ExPublish* pub,
-                    cudaStream_t s) {
+                    cudaStream_t s, void* host_mirror) {
   static const ExPublish none = {};
   const ExPublish& p = pub ? *pub : none;
   launch_dependent(summary_kernel, dim3(1), dim3(p.world ? kMaxWorld : 1), s, static_cast<const DevScalars*>(dev_scalars), mode,
-                   want_lines, summary, p);
+                   want_lines, summary, p, static_cast<DevScalars*>(host_mirror));
 }
 
 void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, uint32_t stride, uint32_t rank,
@@ -314,10 +320,11 @@ void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, 
 
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
                         uint64_t* out_b, unsigned long long* total_b, uint64_t n, unsigned long long* desc,
-                        unsigned int* tickets, uint32_t epoch, cudaStream_t s) {
+                        unsigned int* tickets, uint32_t epoch, cudaStream_t s, unsigned long long* host_total_a) {
   if (n == 0) return;
   const uint64_t nblk = div_up(n, kExTile);
   Scan2 a{};
+  a.host_total = host_total_a;
   a.in[0] = in_a; a.out[0] = out_a; a.total[0] = total_a;
   a.in[1] = in_b; a.out[1] = out_b; a.total[1] = total_b;
   const unsigned tables = in_b ? 2 : 1;

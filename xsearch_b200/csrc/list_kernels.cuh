@@ -28,7 +28,7 @@ void launch_reduce_u32(const uint32_t* in, uint64_t n, unsigned long long* out, 
 // with `epoch`, see lookback()), tickets two zeroed counters.  The tables must be 16-byte aligned.
 void launch_exscan2_u32(const uint32_t* in_a, uint64_t* out_a, unsigned long long* total_a, const uint32_t* in_b,
                         uint64_t* out_b, unsigned long long* total_b, uint64_t n, unsigned long long* desc,
-                        unsigned int* tickets, uint32_t epoch, cudaStream_t s);
+                        unsigned int* tickets, uint32_t epoch, cudaStream_t s, unsigned long long* host_total_a = nullptr);
 
 // *flag = 1 if two consecutive entries of the sorted occurrence list are closer than m (overlapping occurrences)
 void launch_overlap_check(const uint64_t* occ, uint64_t k, uint32_t m, unsigned int* flag, cudaStream_t s);
@@ -73,7 +73,8 @@ void launch_add_u64_from_table(uint64_t* v, uint64_t n, const uint64_t* table, u
 // 3: direct path whose tail replay ran list-free on the side stream (zone_sub / zone_add; a difference means redo)
 // pub (may be nullptr): the kernel also stores the summary into every rank's exchange table and releases the round
 // (xsg_exchange.cu) -- unless a fall-back pass will follow (overlap seen / tail drops), whose summary publishes instead
+// host_mirror (may be nullptr): DevScalars in mapped host memory that receives a copy of the scalars
 void launch_summary(const void* dev_scalars, int mode, int want_lines, unsigned long long* summary, const ExPublish* pub,
-                    cudaStream_t s);
+                    cudaStream_t s, void* host_mirror = nullptr);
 
 }  // namespace xsg

@@ -84,7 +84,8 @@ static int init_ctx(xsg_ctx* c, int device) {
   XSG_CUDA(cudaMalloc(&c->d_scalars, sizeof(DevScalars)));
   XSG_CUDA(cudaMalloc(&c->d_summary, 4 * sizeof(unsigned long long)));
   XSG_CUDA(cudaMemset(c->d_summary, 0, 4 * sizeof(unsigned long long)));
-  XSG_CUDA(cudaHostAlloc(&c->h_scalars, sizeof(DevScalars), cudaHostAllocDefault));
+  XSG_CUDA(cudaHostAlloc(&c->h_scalars, sizeof(DevScalars), cudaHostAllocMapped));
+  XSG_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->d_h_scalars), c->h_scalars, 0));
   XSG_CUDA(cudaMalloc(&c->d_konst, 12 * sizeof(uint32_t)));
   XSG_CUDA(cudaHostAlloc(&c->h_konst, 12 * sizeof(uint32_t), cudaHostAllocDefault));
   XSG_CUDA(cudaHostAlloc(&c->h_ex_bad, sizeof(unsigned int), cudaHostAllocMapped));

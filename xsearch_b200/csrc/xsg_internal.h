@@ -51,7 +51,8 @@ struct xsg_ctx {
   cudaEvent_t stage_copied[2] = {}, stage_free[2] = {};
   xsg::DevScalars* d_scalars = nullptr;
   unsigned long long* d_summary = nullptr;  // {newlines, matches, matching lines, lines} of the last scan
-  xsg::DevScalars* h_scalars = nullptr;  // pinned
+  xsg::DevScalars* h_scalars = nullptr;  // pinned and mapped: the scan's kernels store into it (d_h_scalars)
+  xsg::DevScalars* d_h_scalars = nullptr;  // h_scalars as the device addresses it
   uint32_t* d_konst = nullptr;           // 12 words: the scan kernel's constants in global memory (see ScanArgs::konst)
   uint32_t* h_konst = nullptr;           // pinned staging of the same (= what d_konst holds once konst_valid)
   bool konst_valid = false;

@@ -157,10 +157,10 @@ int next_epoch(xsg_ctx* ctx, uint32_t* out) {
   return XSG_OK;
 }
 
+// The scan's last kernel (summary_kernel) has stored the scalars into the mapped host mirror; ev[3], recorded behind it,
+// says when they are there.  (Was: a D2H copy + an event of its own -- one more trip through a copy engine per scan.)
 int read_scalars(xsg_ctx* ctx) {
-  XSG_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, sizeof(DevScalars), cudaMemcpyDeviceToHost, ctx->stream));
-  XSG_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
-  XSG_CUDA(wait_event(ctx->ev[5]));
+  XSG_CUDA(wait_event(ctx->ev[3]));
   return XSG_OK;
 }
 
@@ -217,7 +217,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     launch_reduce_u32(a.gran_count, n_gran, &ds->occ_total, s);
     launch_zone_count(buf, n, d_bounds, nb, pat, a.gran_count, &ds->zone_sub, &ds->zone_add, s);
     XSG_CUDA(cudaGetLastError());
-    launch_summary(ds, 1, 0, ctx->d_summary, pub, s);
+    launch_summary(ds, 1, 0, ctx->d_summary, pub, s, ctx->d_h_scalars);
     st->launches += 3 + (pat.m > 1 ? 1 : 0);
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
@@ -272,13 +272,12 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
     }
     launch_exscan2_u32(a.gran_count, ctx->gran_prefix.as<uint64_t>(), &ds->occ_total, a.nl_granule,
                        want_idx ? ctx->nl_prefix.as<uint64_t>() : nullptr, &ds->nl_total, n_gran, scan_desc,
-                       &ds->ticket[0], epoch, s);
+                       &ds->ticket[0], epoch, s, &ctx->d_h_scalars->occ_total);
     XSG_CUDA(cudaGetLastError());
     st->launches += 2;
     // pass 2: positions of the occurrences, expanded from the masks of the granules that hold any.
-    // The host needs their number (allocation sizes, grids).
-    XSG_CUDA(cudaMemcpyAsync(&ctx->h_scalars->occ_total, &ds->occ_total, sizeof(unsigned long long),
-                             cudaMemcpyDeviceToHost, s));
+    // The host needs their number (allocation sizes, grids): the prefix-sum kernel has stored it into the mapped host
+    // mirror, the event says when (no copy-engine operation between the prefix sums and pass 2).
     XSG_CUDA(cudaEventRecord(ctx->ev[4], s));
     uint64_t k = 0;
     uint64_t* occ_list = nullptr;
@@ -406,7 +405,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       }
     }
     if (zone_aside) XSG_CUDA(cudaStreamWaitEvent(s, ctx->ev_join, 0));
-    launch_summary(ds, zone_aside ? 3 : (direct ? 2 : 0), (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s);
+    launch_summary(ds, zone_aside ? 3 : (direct ? 2 : 0), (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s, ctx->d_h_scalars);
     st->launches += 1;
     XSG_CUDA(cudaEventRecord(ctx->ev[3], s));
     if ((rc = read_scalars(ctx))) return rc;
@@ -432,7 +431,7 @@ int scan_device(xsg_ctx* ctx, const uint8_t* buf, uint64_t n, const uint64_t* d_
       c.unterminated = &ds->unterminated;
       launch_compact(c, pat, s);
       XSG_CUDA(cudaGetLastError());
-      launch_summary(ds, 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s);
+      launch_summary(ds, 0, (kinds & XSG_LINES) ? 1 : 0, ctx->d_summary, pub, s, ctx->d_h_scalars);
       st->launches += 4;
       XSG_CUDA(cudaFreeAsync(part->match_off, s));
       part->match_off = fixed;
