@@ -713,21 +713,46 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const uint64_t n_gran = a.n_tiles * kWarps;
-  // one warp per unit of 32 granules: the serial part of a warp is the handful of hit granules of its unit
-  const uint64_t g0 = ((uint64_t)blockIdx.x * kWarps + warp) * 32;
-  if (g0 >= n_gran) return;
-  const uint64_t gi = g0 + lane;
-  const uint32_t c = gi < n_gran ? a.gran_count[gi] : 0;
-  if (c == 1) {  // no mask for a single occurrence: pass 1 left its position in gran_first
-    const unsigned long long slot = a.gran_prefix[gi];
-    if (slot < a.occ_cap) a.occ[slot] = gi * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add + a.gran_first[gi];
+  // one warp per unit of 32 granules: the serial part of a warp is the handful of hit granules of its unit.  The sparse
+  // variant takes kUnits units per warp and loads their counters -- then the slots and positions of their single-hit
+  // granules -- side by side: with one 4-byte load per lane in flight the kernel was bound by memory latency.
+  constexpr int kUnits = PAIRS ? 1 : 4;
+  const uint64_t gw = ((uint64_t)blockIdx.x * kWarps + warp) * (32 * kUnits);
+  if (gw >= n_gran) return;
+  uint32_t cu[kUnits];
+#pragma unroll
+  for (int u = 0; u < kUnits; ++u) {
+    const uint64_t gi = gw + 32 * u + lane;
+    cu[u] = gi < n_gran ? a.gran_count[gi] : 0;
   }
+  {  // no mask for a single occurrence: pass 1 left its position in gran_first
+    unsigned long long slot[kUnits];
+    uint32_t first[kUnits];
+#pragma unroll
+    for (int u = 0; u < kUnits; ++u) {
+      const uint64_t gi = gw + 32 * u + lane;
+      slot[u] = cu[u] == 1 ? a.gran_prefix[gi] : ~0ull;
+      first[u] = cu[u] == 1 ? a.gran_first[gi] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < kUnits; ++u) {
+      const uint64_t gi = gw + 32 * u + lane;
+      if (cu[u] == 1 && slot[u] < a.occ_cap) a.occ[slot[u]] = gi * (uint64_t)kGranuleBytes - pat.anchor + a.occ_add + first[u];
+    }
+  }
+#pragma unroll 1
+  for (int u = 0; u < kUnits; ++u) {
+  const uint64_t g0 = gw + 32 * u;
+  const uint64_t gi = g0 + lane;
+  uint32_t c = cu[0];
+#pragma unroll
+  for (int v = 1; v < kUnits; ++v) c = u == v ? cu[v] : c;
   unsigned todo = __ballot_sync(kFull, c > 1);
-  if (todo == 0) return;
+  if (todo == 0) continue;
   if (todo == kFull) {  // every granule of the unit holds several occurrences: the dense case, as a straight loop
     if (PAIRS) emit_dense_unit(pat, a, g0, lane, s_queue[warp], s_stage[warp]);
     else emit_dense_unit1(pat, a, g0, lane, s_queue[warp], s_stage[warp]);
-    return;
+    continue;
   }
   // lane i fetches the output base of granule g0 + i (one coalesced load, handed out by shuffle below).  The
   // masks are expanded one granule after the other with the next one in flight; to make that next load an L2
@@ -792,6 +817,7 @@ emit_kernel(const __grid_constant__ Pattern pat, const __grid_constant__ ScanArg
       __syncwarp();  // stage and queue are rewritten for the next hit granule
     }
   }
+  }  // units
 }
 
 inline bool staged_enabled() {
@@ -845,10 +871,10 @@ cudaError_t launch_count(const Pattern& pat, const ScanArgs& a, bool newlines, b
 
 cudaError_t launch_emit(const Pattern& pat, const ScanArgs& a, bool dense, cudaStream_t s) {
   if (a.n_tiles == 0) return cudaSuccess;
-  const uint64_t units = div_up(a.n_tiles * kWarps, 32);  // units of 32 granules, one warp each
-  const dim3 grid((unsigned)div_up(units, kWarps)), block(kThreads);
-  if (dense) launch_dependent(emit_kernel<true>, grid, block, s, pat, a);
-  else launch_dependent(emit_kernel<false>, grid, block, s, pat, a);
+  const uint64_t units = div_up(a.n_tiles * kWarps, 32);  // units of 32 granules: one per warp (dense), four per warp (sparse)
+  const dim3 block(kThreads);
+  if (dense) launch_dependent(emit_kernel<true>, dim3((unsigned)div_up(units, kWarps)), block, s, pat, a);
+  else launch_dependent(emit_kernel<false>, dim3((unsigned)div_up(units, 4 * kWarps)), block, s, pat, a);
   return cudaGetLastError();
 }
 
