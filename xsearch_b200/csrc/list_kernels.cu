@@ -144,7 +144,7 @@ struct Scan2 {
 constexpr int kExItems = 32;
 constexpr int kExTile = kScanThreads * kExItems;
 
-__global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_constant__ Scan2 a, uint64_t n, uint64_t nblk,
+__global__ void __launch_bounds__(kScanThreads, 5) exscan_kernel(const __grid_constant__ Scan2 a, uint64_t n, uint64_t nblk,
                                                               unsigned long long* desc_all, unsigned int* tickets,
                                                               uint32_t epoch) {
   __shared__ unsigned int s_tile;
@@ -162,10 +162,11 @@ __global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_const
   const bool full = base + kExItems <= n;
   if (full) {
 #pragma unroll
-    for (int i = 0; i < kExItems / 4; ++i) {
-      const uint4 p = *reinterpret_cast<const uint4*>(in + base + 4 * i);
-      x[4 * i] = p.x; x[4 * i + 1] = p.y; x[4 * i + 2] = p.z; x[4 * i + 3] = p.w;
-    }
+    for (int i = 0; i < kExItems / 8; ++i)  // 32 bytes per load, 64 per store: a thread's items are contiguous, its
+      asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"  // neighbours' are 128 / 256 bytes away
+                   : "=r"(x[8 * i]), "=r"(x[8 * i + 1]), "=r"(x[8 * i + 2]), "=r"(x[8 * i + 3]), "=r"(x[8 * i + 4]),
+                     "=r"(x[8 * i + 5]), "=r"(x[8 * i + 6]), "=r"(x[8 * i + 7])
+                   : "l"(in + base + 8 * i));
   } else {
 #pragma unroll
     for (int i = 0; i < kExItems; ++i) x[i] = base + i < n ? in[base + i] : 0;
@@ -191,12 +192,12 @@ __global__ void __launch_bounds__(kScanThreads) exscan_kernel(const __grid_const
   __syncthreads();
   uint64_t run = s_base + local;
   if (full) {
-    ulonglong2* o = reinterpret_cast<ulonglong2*>(out + base);
+    uint64_t* o = out + base;
 #pragma unroll
-    for (int i = 0; i < kExItems / 2; ++i) {
-      const uint64_t r0 = run, r1 = run + x[2 * i];
-      run = r1 + x[2 * i + 1];
-      o[i] = make_ulonglong2(r0, r1);
+    for (int i = 0; i < kExItems / 4; ++i) {
+      const uint64_t r0 = run, r1 = r0 + x[4 * i], r2 = r1 + x[4 * i + 1], r3 = r2 + x[4 * i + 2];
+      run = r3 + x[4 * i + 3];
+      asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" ::"l"(o + 4 * i), "l"(r0), "l"(r1), "l"(r2), "l"(r3) : "memory");
     }
     if (base + kExItems == n) out[n] = run;
   } else {
