@@ -1,5 +1,6 @@
 #!/bin/bash
-# same-box A/B of builds of libxsg.so: every tools/ab/libxsg_<name>.so (through XSG_LIB) and the in-tree one ("new"),
+# same-box A/B of builds of libxsg.so: every tools/ab/libxsg_<name>.so (copies of earlier builds, git-ignored; loaded
+# through XSG_LIB) and the in-tree one ("new"),
 # interleaved, AB_REPS rounds.  usage: tools/r2_ab.sh [bench.py args]      (results: gpurun_out/ab_*.json)
 mkdir -p gpurun_out
 sides="$(ls tools/ab/libxsg_*.so 2>/dev/null | sed 's/.*libxsg_\(.*\)\.so/\1/') new"
